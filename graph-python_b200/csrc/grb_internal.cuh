@@ -1,0 +1,208 @@
+// grb_internal.cuh — object model, device memory and error plumbing of libgrb_b200.so.
+//
+// Design (B200-first, not a SuiteSparse port):
+//   * every GrB_Matrix lives in HBM as CSR with 64-bit row pointers, 32-bit column indices and typed
+//     (or iso) values; a transposed copy (CSR of A') is built lazily on the device and cached, so each
+//     product can run in its bandwidth-friendly direction (pull = streaming, push = sparse frontier);
+//   * every GrB_Vector lives in HBM as a dense value array + presence bytes (the GxB bitmap format),
+//     double-buffered so `w(accum) << w.vxm(A)` ping-pongs without allocation, with an optional sorted
+//     index list (the sparse frontier) and a device-side nvals counter;
+//   * Scalar / Vector / Matrix handles share one struct so the reference's pointer casts
+//     (Vector._as_matrix, reference graphblas/core/vector.py:194-202) stay legal;
+//   * all work is enqueued on one CUDA stream (default: the legacy default stream, which is torch's
+//     current stream unless changed; GxB_b200_set_stream overrides); the host only synchronises when a
+//     value must cross the ABI (nvals, extract*, export*, wait).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/GraphBLAS_b200.h"
+
+// ---- codes (type codes match tools/gen_abi.py; op codes match oracle/grb_oracle.c) ----
+enum TypeCode { TC_BOOL = 0, TC_INT8, TC_INT16, TC_INT32, TC_INT64, TC_UINT8, TC_UINT16, TC_UINT32,
+                TC_UINT64, TC_FP32, TC_FP64, TC_COUNT };
+enum OpCode { OP_FIRST = 0, OP_SECOND, OP_ONEB, OP_ANY, OP_PLUS, OP_MINUS, OP_TIMES, OP_DIV, OP_MIN, OP_MAX,
+              OP_LOR, OP_LAND, OP_LXOR, OP_LXNOR, OP_EQ, OP_NE, OP_GT, OP_LT, OP_GE, OP_LE, OP_COUNT };
+enum IdxOp { IDX_TRIL = 0, IDX_TRIU, IDX_DIAG, IDX_OFFDIAG };
+enum ObjKind { K_SCALAR = 0, K_VECTOR = 1, K_MATRIX = 2 };
+
+static const size_t kTypeSize[TC_COUNT] = {1, 1, 2, 4, 8, 1, 2, 4, 8, 4, 8};
+
+struct GB_Type_opaque { int code; size_t size; const char *name; };
+struct GB_UnaryOp_opaque { int op; int tcode; const char *name; };
+struct GB_IndexUnaryOp_opaque { int op; const char *name; };
+struct GB_BinaryOp_opaque { int op; int xcode; int zcode; const char *name; };
+struct GB_Monoid_opaque { int op; int tcode; const char *name; };
+struct GB_Semiring_opaque { int mon; int mul; int tcode; const char *name; };
+
+#define GRB_MAGIC 0x42323030u   /* "B200" */
+#define GRB_FREED 0x46524545u
+
+struct GB_Descriptor_opaque {
+    uint32_t magic = GRB_MAGIC;
+    bool replace = false, comp = false, structure = false, tran0 = false, tran1 = false;
+    int axb_method = 0;  // GxB_DEFAULT / GUSTAVSON / DOT / HASH / SAXPY (a hint; results identical)
+    bool builtin = false;
+    std::string err;
+};
+
+// CSR block in HBM.  rowptr int64[nrows+1]; colidx uint32[nnz] sorted within rows; vals type[nnz] or [1] if iso.
+struct Csr {
+    int64_t nrows = 0, ncols = 0, nnz = 0;
+    int64_t *rowptr = nullptr;
+    uint32_t *colidx = nullptr;
+    void *vals = nullptr;
+    bool iso = false;
+    // tile metadata for the streaming SpMV (first owned row of every nnz tile), built lazily
+    int32_t *tile_row = nullptr;
+    int64_t ntiles = 0;
+    int tile_nnz = 0;
+};
+
+struct GB_Object {
+    uint32_t magic = GRB_MAGIC;
+    int kind = K_MATRIX;
+    GrB_Type type = nullptr;
+    int64_t nrows = 0, ncols = 0;
+    // ---- matrix storage ----
+    Csr csr;             // A by rows
+    Csr csc;             // A' by rows (== A by columns), valid iff csc_valid
+    bool csc_valid = false;
+    // ---- dense vector / scalar storage (n = nrows) ----
+    void *vals = nullptr;
+    uint8_t *present = nullptr;
+    void *vals_alt = nullptr;        // ping-pong spares (lazily allocated)
+    uint8_t *present_alt = nullptr;
+    int64_t nvals = 0;               // host copy, valid iff nvals_known
+    bool nvals_known = true;
+    int64_t *d_nvals = nullptr;      // device counter written by the producing kernel
+    uint32_t *list = nullptr;        // sorted indices of present entries (sparse frontier), iff list_valid
+    int64_t list_cap = 0;
+    bool list_valid = false;
+    std::string err;
+};
+struct GB_Matrix_opaque : GB_Object {};
+struct GB_Vector_opaque : GB_Object {};
+struct GB_Scalar_opaque : GB_Object {};
+
+struct GrbError {
+    GrB_Info info;
+    std::string msg;
+};
+[[noreturn]] inline void grb_throw(GrB_Info info, const std::string &msg) { throw GrbError{info, msg}; }
+
+#define CUDA_TRY(expr)                                                                             \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            GrB_Info _i = (_e == cudaErrorMemoryAllocation) ? GrB_OUT_OF_MEMORY : GrB_PANIC;       \
+            char _b[512];                                                                          \
+            snprintf(_b, sizeof _b, "CUDA error %s at %s:%d (%s)", cudaGetErrorName(_e), __FILE__, \
+                     __LINE__, cudaGetErrorString(_e));                                            \
+            cudaGetLastError();                                                                    \
+            grb_throw(_i, _b);                                                                     \
+        }                                                                                          \
+    } while (0)
+
+struct GrbGlobal {
+    bool initialized = false;
+    bool blocking = false;
+    int device = -1;
+    int sm_count = 148;
+    cudaStream_t stream = 0;
+    void *(*h_malloc)(size_t) = malloc;
+    void (*h_free)(void *) = free;
+    uint64_t launches = 0;
+    const char *last_kernel = "";
+    // tunables (GxB_b200_set_option)
+    int64_t push_ratio = 24;       // push when nvals(u) * push_ratio < n
+    int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
+    int64_t burble = 0;
+    // scratch
+    int64_t *d_scratch = nullptr;  // 64 int64 of device scratch (counters)
+    int64_t *h_pinned = nullptr;   // 64 int64 of pinned host memory for small read-backs
+};
+extern GrbGlobal g;
+
+// every kernel launch goes through this macro: counts launches (bench.py's gpu_launches) and names the path
+#define GRB_LAUNCH(name, kernel, grid, block, smem, ...)                             \
+    do {                                                                             \
+        kernel<<<(grid), (block), (smem), g.stream>>>(__VA_ARGS__);                  \
+        g.launches++;                                                                \
+        g.last_kernel = name;                                                        \
+        if (g.burble) fprintf(stderr, "[grb_b200] %s grid=%lld block=%d\n", name, (long long)(grid), (int)(block)); \
+        CUDA_TRY(cudaGetLastError());                                                \
+    } while (0)
+
+// ---- device memory (stream-ordered pool) ----
+void *dmalloc(size_t bytes);
+void dfree(void *p);
+template <class T> inline T *dalloc(int64_t n) { return (T *)dmalloc((size_t)(n > 0 ? n : 1) * sizeof(T)); }
+void h2d(void *dst, const void *src, size_t bytes);
+void d2h(void *dst, const void *src, size_t bytes);
+void d2d(void *dst, const void *src, size_t bytes);
+void dzero(void *dst, size_t bytes);
+void stream_sync();
+int64_t read_i64(const int64_t *dptr);   // synchronising read-back of one device int64
+
+// ---- object helpers (grb_containers.cu) ----
+GB_Object *obj_check(const void *h, const char *what);   // NULL -> GrB_NULL_POINTER, bad magic -> INVALID_OBJECT
+void csr_free(Csr &c);
+void obj_release_storage(GB_Object *o);
+void obj_invalidate_caches(GB_Object *o);                 // after the CSR changed: drop csc + tiles
+void vec_alloc(GB_Object *o);                             // allocate dense storage (zeroed presence)
+void vec_ensure_alt(GB_Object *o);
+int64_t vec_nvals(GB_Object *o);                          // syncs if the count is still on the device
+void vec_set_unknown_nvals(GB_Object *o);                 // producer kernels wrote d_nvals
+void vec_build_list(GB_Object *o);                        // dense -> sorted index list (device compaction)
+void mat_ensure_csc(GB_Object *o);                        // build + cache the transpose on the device
+void csr_transpose(const Csr &a, Csr &t, size_t tsize);
+void csr_ensure_tiles(Csr &c, int tile_nnz);
+void mat_set_csr(GB_Object *o, Csr &c);                   // take ownership of c as o's CSR
+Csr csr_dup(const Csr &a, size_t tsize);
+Csr vec_as_csr_column(GB_Object *v);                      // n x 1 matrix view of a vector (copy)
+Csr vec_as_csr_row(GB_Object *v);                         // 1 x n
+void csr_to_vec(const Csr &c, GB_Object *v, bool as_column);
+void csr_cast_values(Csr &c, int from_code, int to_code);
+
+// API boundary: catch GrbError, stash the message on the first object for GrB_*_error
+#define API_BEGIN try {
+#define API_END(errobj)                                                          \
+    }                                                                            \
+    catch (const GrbError &e) {                                                  \
+        GB_Object *_o = (GB_Object *)(errobj);                                   \
+        if (_o && _o->magic == GRB_MAGIC) _o->err = e.msg;                       \
+        if (g.burble) fprintf(stderr, "[grb_b200] error %d: %s\n", (int)e.info, e.msg.c_str()); \
+        return e.info;                                                           \
+    }                                                                            \
+    catch (const std::bad_alloc &) { return GrB_OUT_OF_MEMORY; }                 \
+    return GrB_SUCCESS;
+
+inline void require_init() {
+    if (!g.initialized) grb_throw(GrB_PANIC, "GrB_init has not been called (or no CUDA device: libgrb_b200 has no CPU fallback)");
+}
+
+// ---- type dispatch: binds T to the C++ type of a type code ----
+#define GRB_TYPE_SWITCH(code, T, ...)                                              \
+    switch (code) {                                                                \
+    case TC_BOOL: { using T = bool; __VA_ARGS__; } break;                          \
+    case TC_INT8: { using T = int8_t; __VA_ARGS__; } break;                        \
+    case TC_INT16: { using T = int16_t; __VA_ARGS__; } break;                      \
+    case TC_INT32: { using T = int32_t; __VA_ARGS__; } break;                      \
+    case TC_INT64: { using T = int64_t; __VA_ARGS__; } break;                      \
+    case TC_UINT8: { using T = uint8_t; __VA_ARGS__; } break;                      \
+    case TC_UINT16: { using T = uint16_t; __VA_ARGS__; } break;                    \
+    case TC_UINT32: { using T = uint32_t; __VA_ARGS__; } break;                    \
+    case TC_UINT64: { using T = uint64_t; __VA_ARGS__; } break;                    \
+    case TC_FP32: { using T = float; __VA_ARGS__; } break;                         \
+    case TC_FP64: { using T = double; __VA_ARGS__; } break;                        \
+    default: grb_throw(GrB_INVALID_VALUE, "unknown type code");                    \
+    }
+
+inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -1,0 +1,418 @@
+// grb_storage.cu — device-side storage plumbing: COO -> CSR build (sort + dedup with dup op), transpose,
+// vector <-> n x 1 / 1 x n CSR conversions, index narrowing, SpMV tile metadata.
+// This is ingest / format plumbing, not the hot loop; the sort and
+// scan primitives come from CUB (shipped with the CUDA toolkit), everything else is written here.
+#include <cub/cub.cuh>
+
+#include "grb_internal.cuh"
+#include "grb_ops.cuh"
+#include "grb_storage.cuh"
+
+// ---------------------------------------------------------------- small kernels
+__global__ void k_iota_u32(uint32_t *p, int64_t n) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) p[i] = (uint32_t)i;
+}
+__global__ void k_make_keys(const uint64_t *I, const uint64_t *J, uint64_t nrows, uint64_t ncols, int64_t n,
+                            uint64_t *keys, int *bad) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint64_t i = I[k], j = J ? J[k] : 0;
+    if (i >= nrows || j >= ncols) { *bad = 1; keys[k] = 0; return; }
+    keys[k] = i * ncols + j;
+}
+__global__ void k_head_flags(const uint64_t *keys, int64_t n, int64_t *flag) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k < n) flag[k] = (k == 0 || keys[k] != keys[k - 1]) ? 1 : 0;
+}
+// one thread per distinct key: fold its duplicates in input order with the dup op, emit col + value
+template <class T>
+__global__ void k_dedup(const uint64_t *keys, const uint32_t *perm, const int64_t *pos, int64_t n,
+                        const T *vin, int iso_in, int dup_op, uint64_t ncols, uint32_t *col_out,
+                        uint32_t *row_out, T *vout, int *dup_seen) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    if (k != 0 && keys[k] == keys[k - 1]) return;
+    uint64_t key = keys[k];
+    T acc = vin ? vin[iso_in ? 0 : perm[k]] : (T)0;
+    int64_t q = k + 1;
+    while (q < n && keys[q] == key) {
+        if (dup_op < 0) *dup_seen = 1;
+        else if (vin) acc = binop_rt<T>(dup_op, acc, vin[iso_in ? 0 : perm[q]]);
+        q++;
+    }
+    int64_t o = pos[k];
+    col_out[o] = (uint32_t)(key % ncols);
+    row_out[o] = (uint32_t)(key / ncols);
+    if (vout) vout[o] = acc;
+}
+// rowptr from sorted row ids: rowptr[r] = first entry whose row >= r
+__global__ void k_rowptr_from_rows(const uint32_t *rows, int64_t nnz, int64_t nrows, int64_t *rowptr) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k > nnz) return;
+    int64_t lo = (k == 0) ? 0 : (int64_t)rows[k - 1] + 1;
+    int64_t hi = (k == nnz) ? nrows : (int64_t)rows[k];
+    for (int64_t r = lo; r <= hi; r++) rowptr[r] = k;
+}
+__global__ void k_expand_rows(const int64_t *rowptr, int64_t nrows, uint32_t *rows) {
+    // one warp per row
+    int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (w >= nrows) return;
+    for (int64_t p = rowptr[w] + lane; p < rowptr[w + 1]; p += 32) rows[p] = (uint32_t)w;
+}
+__global__ void k_transpose_keys(const uint32_t *rows, const uint32_t *cols, int64_t nnz, uint64_t nrows,
+                                 uint64_t *keys) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k < nnz) keys[k] = (uint64_t)cols[k] * nrows + rows[k];
+}
+__global__ void k_narrow_u64(const uint64_t *in, int64_t n, uint32_t *out, uint64_t bound, int *bad) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint64_t v = in[k];
+    if (v >= bound) *bad = 1;
+    out[k] = (uint32_t)v;
+}
+__global__ void k_widen_u32(const uint32_t *in, int64_t n, uint64_t *out) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k < n) out[k] = in[k];
+}
+__global__ void k_check_csr(const int64_t *rowptr, const uint32_t *col, int64_t nrows, int64_t nnz, int *flags) {
+    // flags[0]: rowptr not monotone / out of range; flags[1]: some row unsorted or with duplicates
+    int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (w >= nrows) return;
+    int64_t a = rowptr[w], b = rowptr[w + 1];
+    if (a > b || a < 0 || b > nnz) { flags[0] = 1; return; }
+    for (int64_t p = a + 1 + lane; p < b; p += 32)
+        if (col[p] <= col[p - 1]) flags[1] = 1;
+}
+template <class T>
+__global__ void k_gather(const T *in, const uint32_t *perm, int64_t n, T *out) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k < n) out[k] = in[perm[k]];
+}
+
+static inline int nblk(int64_t n, int b = 256) { return (int)cdiv(n > 0 ? n : 1, b); }
+
+// ---------------------------------------------------------------- COO -> CSR
+// keys = row*ncols+col (device, unsorted, n of them); vals may be null (pattern only) or iso (1 value).
+// dup_op >= 0: fold duplicates; dup_op == -1: duplicates are an error; result rows sorted, no duplicates.
+Csr coo_to_csr(int64_t nrows, int64_t ncols, uint64_t *keys, const void *vals, bool iso_in, int tcode,
+               int64_t n, int dup_op, bool keep_iso) {
+    Csr c;
+    c.nrows = nrows; c.ncols = ncols;
+    size_t tsize = kTypeSize[tcode];
+    c.rowptr = dalloc<int64_t>(nrows + 1);
+    if (n == 0) {
+        dzero(c.rowptr, (size_t)(nrows + 1) * sizeof(int64_t));
+        c.colidx = dalloc<uint32_t>(1);
+        c.vals = dmalloc(tsize);
+        return c;
+    }
+    uint64_t *keys2 = dalloc<uint64_t>(n);
+    uint32_t *perm = dalloc<uint32_t>(n), *perm2 = dalloc<uint32_t>(n);
+    GRB_LAUNCH("iota", k_iota_u32, nblk(n), 256, 0, perm, n);
+    int bits = 1;
+    {
+        unsigned __int128 span = (unsigned __int128)(uint64_t)nrows * (uint64_t)(ncols > 0 ? ncols : 1);
+        while (bits < 64 && ((unsigned __int128)1 << bits) < span) bits++;
+    }
+    size_t tmp_bytes = 0;
+    cub::DoubleBuffer<uint64_t> dk(keys, keys2);
+    cub::DoubleBuffer<uint32_t> dv(perm, perm2);
+    CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, n, 0, bits, g.stream));
+    void *tmp = dmalloc(tmp_bytes);
+    CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, n, 0, bits, g.stream));
+    g.launches += 2 * ((bits + 7) / 8);
+    dfree(tmp);
+    uint64_t *sk = dk.Current();
+    uint32_t *sp = dv.Current();
+    // distinct keys -> output positions
+    int64_t *flag = dalloc<int64_t>(n + 1), *pos = dalloc<int64_t>(n + 1);
+    GRB_LAUNCH("head_flags", k_head_flags, nblk(n), 256, 0, sk, n, flag);
+    dzero(flag + n, sizeof(int64_t));
+    tmp_bytes = 0;
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, flag, pos, n + 1, g.stream));
+    tmp = dmalloc(tmp_bytes);
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, flag, pos, n + 1, g.stream));
+    g.launches += 2;
+    dfree(tmp);
+    int64_t nnz = read_i64(pos + n);
+    c.nnz = nnz;
+    c.colidx = dalloc<uint32_t>(nnz);
+    uint32_t *rows = dalloc<uint32_t>(nnz);
+    bool iso_out = keep_iso && iso_in;
+    c.iso = iso_out;
+    c.vals = dmalloc(iso_out ? tsize : (size_t)(nnz > 0 ? nnz : 1) * tsize);
+    int *dflag = (int *)g.d_scratch;
+    dzero(dflag, sizeof(int));
+    GRB_TYPE_SWITCH(tcode, T,
+        GRB_LAUNCH("dedup", k_dedup<T>, nblk(n), 256, 0, sk, sp, pos, n, (const T *)vals, (int)iso_in,
+                   dup_op, (uint64_t)(ncols > 0 ? ncols : 1), c.colidx, rows,
+                   iso_out ? (T *)nullptr : (T *)c.vals, dflag));
+    if (iso_out && vals) d2d(c.vals, vals, tsize);
+    GRB_LAUNCH("rowptr", k_rowptr_from_rows, nblk(nnz + 1), 256, 0, rows, nnz, nrows, c.rowptr);
+    int hflag = 0;
+    d2h(&hflag, dflag, sizeof(int));
+    stream_sync();
+    dfree(rows); dfree(flag); dfree(pos); dfree(keys2); dfree(perm); dfree(perm2);
+    if (hflag) {
+        csr_free(c);
+        grb_throw(GrB_INVALID_VALUE, "duplicate indices in build and no dup_op given");
+    }
+    return c;
+}
+
+// ---------------------------------------------------------------- helpers on CSR
+void csr_free(Csr &c) {
+    dfree(c.rowptr); dfree(c.colidx); dfree(c.vals); dfree(c.tile_row);
+    c = Csr();
+}
+
+uint32_t *csr_row_ids(const Csr &c) {
+    uint32_t *rows = dalloc<uint32_t>(c.nnz);
+    if (c.nnz) GRB_LAUNCH("expand_rows", k_expand_rows, nblk(c.nrows * 32), 256, 0, c.rowptr, c.nrows, rows);
+    return rows;
+}
+
+void narrow_indices(const uint64_t *d_in, int64_t n, uint32_t *d_out, uint64_t bound, const char *what) {
+    if (n == 0) return;
+    int *dflag = (int *)g.d_scratch;
+    dzero(dflag, sizeof(int));
+    GRB_LAUNCH("narrow", k_narrow_u64, nblk(n), 256, 0, d_in, n, d_out, bound, dflag);
+    int h = 0;
+    d2h(&h, dflag, sizeof(int));
+    stream_sync();
+    if (h) grb_throw(GrB_INDEX_OUT_OF_BOUNDS, std::string("index out of bounds in ") + what);
+}
+void widen_indices(const uint32_t *d_in, int64_t n, uint64_t *d_out) {
+    if (n) GRB_LAUNCH("widen", k_widen_u32, nblk(n), 256, 0, d_in, n, d_out);
+}
+
+bool csr_is_sorted(const Csr &c) {
+    if (c.nnz == 0) return true;
+    int *dflag = (int *)g.d_scratch;
+    dzero(dflag, 2 * sizeof(int));
+    GRB_LAUNCH("check_csr", k_check_csr, nblk(c.nrows * 32), 256, 0, c.rowptr, c.colidx, c.nrows, c.nnz, dflag);
+    int h[2] = {0, 0};
+    d2h(h, dflag, 2 * sizeof(int));
+    stream_sync();
+    if (h[0]) grb_throw(GrB_INVALID_VALUE, "row pointers are not monotone or exceed the index array");
+    return h[1] == 0;
+}
+
+Csr csr_dup(const Csr &a, size_t tsize) {
+    Csr c;
+    c.nrows = a.nrows; c.ncols = a.ncols; c.nnz = a.nnz; c.iso = a.iso;
+    c.rowptr = dalloc<int64_t>(a.nrows + 1);
+    c.colidx = dalloc<uint32_t>(a.nnz);
+    size_t vb = a.iso ? tsize : (size_t)(a.nnz > 0 ? a.nnz : 1) * tsize;
+    c.vals = dmalloc(vb);
+    d2d(c.rowptr, a.rowptr, (size_t)(a.nrows + 1) * sizeof(int64_t));
+    d2d(c.colidx, a.colidx, (size_t)a.nnz * sizeof(uint32_t));
+    d2d(c.vals, a.vals, a.iso ? tsize : (size_t)a.nnz * tsize);
+    return c;
+}
+
+static int tcode_of_size(size_t tsize) {
+    return tsize == 1 ? TC_UINT8 : tsize == 2 ? TC_UINT16 : tsize == 4 ? TC_UINT32 : TC_UINT64;
+}
+
+// t = a' : keys (col*nrows+row) radix-sorted; values moved as opaque words of their size
+void csr_transpose(const Csr &a, Csr &t, size_t tsize) {
+    uint32_t *rows = csr_row_ids(a);
+    uint64_t *keys = dalloc<uint64_t>(a.nnz);
+    if (a.nnz)
+        GRB_LAUNCH("transpose_keys", k_transpose_keys, nblk(a.nnz), 256, 0, rows, a.colidx, a.nnz,
+                   (uint64_t)(a.nrows > 0 ? a.nrows : 1), keys);
+    dfree(rows);
+    t = coo_to_csr(a.ncols, a.nrows, keys, a.vals, a.iso, tcode_of_size(tsize), a.nnz, OP_SECOND, true);
+    dfree(keys);
+}
+
+void csr_sort_rows(Csr &c, int tcode) {
+    uint32_t *rows = csr_row_ids(c);
+    uint64_t *keys = dalloc<uint64_t>(c.nnz);
+    // reuse transpose-key kernel with roles swapped: key = row*ncols + col
+    if (c.nnz)
+        GRB_LAUNCH("sort_keys", k_transpose_keys, nblk(c.nnz), 256, 0, c.colidx, rows, c.nnz,
+                   (uint64_t)(c.ncols > 0 ? c.ncols : 1), keys);
+    dfree(rows);
+    Csr s = coo_to_csr(c.nrows, c.ncols, keys, c.vals, c.iso, tcode, c.nnz, OP_SECOND, true);
+    dfree(keys);
+    csr_free(c);
+    c = s;
+}
+
+// ---------------------------------------------------------------- SpMV tile metadata
+// tile t covers entries [t*TN, (t+1)*TN); tile_row[t] = first row r with rowptr[r] >= t*TN (row "owned"
+// by the tile where it starts).  tile_row[ntiles] = nrows.
+__global__ void k_tile_rows(const int64_t *rowptr, int64_t nrows, int64_t ntiles, int tile_nnz, int32_t *tile_row) {
+    int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    if (t == ntiles) { tile_row[t] = (int32_t)nrows; return; }
+    int64_t target = t * (int64_t)tile_nnz;
+    int64_t lo = 0, hi = nrows;  // first r in [0,nrows] with rowptr[r] >= target
+    while (lo < hi) {
+        int64_t mid = (lo + hi) >> 1;
+        if (rowptr[mid] >= target) hi = mid; else lo = mid + 1;
+    }
+    tile_row[t] = (int32_t)lo;
+}
+void csr_ensure_tiles(Csr &c, int tile_nnz) {
+    if (c.tile_row && c.tile_nnz == tile_nnz) return;
+    dfree(c.tile_row);
+    c.ntiles = c.nnz > 0 ? cdiv(c.nnz, tile_nnz) : 1;
+    c.tile_nnz = tile_nnz;
+    c.tile_row = dalloc<int32_t>(c.ntiles + 1);
+    GRB_LAUNCH("tile_rows", k_tile_rows, nblk(c.ntiles + 1), 256, 0, c.rowptr, c.nrows, c.ntiles, tile_nnz, c.tile_row);
+}
+
+// ---------------------------------------------------------------- dense vector <-> CSR
+__global__ void k_count_present(const uint8_t *p, int64_t n, int64_t *count) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int c = 0;
+    for (; i < n; i += (int64_t)gridDim.x * blockDim.x) c += p[i] ? 1 : 0;
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd((unsigned long long *)count, (unsigned long long)c);
+}
+int64_t count_present(const uint8_t *present, int64_t n, int64_t *d_count) {
+    dzero(d_count, sizeof(int64_t));
+    int blocks = (int)(cdiv(n, 256) < 148 * 8 ? cdiv(n > 0 ? n : 1, 256) : 148 * 8);
+    GRB_LAUNCH("count_present", k_count_present, blocks, 256, 0, present, n, d_count);
+    return 0;
+}
+template <class T>
+__global__ void k_vec_compact(const uint8_t *present, const T *vals, const int64_t *pos, int64_t n,
+                              uint32_t *idx_out, T *val_out) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n || !present[i]) return;
+    int64_t o = pos[i];
+    if (idx_out) idx_out[o] = (uint32_t)i;
+    if (val_out) val_out[o] = vals[i];
+}
+// pos[i] = number of present entries before i; pos has n+1 entries, pos[n] = total
+__global__ void k_present_to_i64(const uint8_t *present, int64_t n, int64_t *flag) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i <= n) flag[i] = (i < n && present[i]) ? 1 : 0;
+}
+static int64_t *present_scan(const uint8_t *present, int64_t n) {
+    int64_t *flag = dalloc<int64_t>(n + 1), *pos = dalloc<int64_t>(n + 1);
+    GRB_LAUNCH("present_flags", k_present_to_i64, nblk(n + 1), 256, 0, present, n, flag);
+    size_t tb = 0;
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tb, flag, pos, n + 1, g.stream));
+    void *tmp = dmalloc(tb);
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(tmp, tb, flag, pos, n + 1, g.stream));
+    g.launches += 2;
+    dfree(tmp); dfree(flag);
+    return pos;
+}
+
+void vec_build_list(GB_Object *o) {
+    if (o->list_valid) return;
+    int64_t n = o->nrows;
+    int64_t *pos = present_scan(o->present, n);
+    int64_t nv = read_i64(pos + n);
+    o->nvals = nv; o->nvals_known = true;
+    if (o->list_cap < nv || !o->list) {
+        dfree(o->list);
+        o->list_cap = nv > 1024 ? nv : 1024;
+        o->list = dalloc<uint32_t>(o->list_cap);
+    }
+    if (nv) GRB_LAUNCH("vec_compact", k_vec_compact<uint8_t>, nblk(n), 256, 0, o->present, (const uint8_t *)nullptr,
+                       pos, n, o->list, (uint8_t *)nullptr);
+    dfree(pos);
+    o->list_valid = true;
+}
+
+Csr vec_as_csr_column(GB_Object *v) {
+    int64_t n = v->nrows;
+    size_t ts = v->type->size;
+    Csr c;
+    c.nrows = n; c.ncols = 1;
+    int64_t *pos = present_scan(v->present, n);
+    c.nnz = read_i64(pos + n);
+    c.rowptr = pos;
+    c.colidx = dalloc<uint32_t>(c.nnz);
+    dzero(c.colidx, (size_t)c.nnz * sizeof(uint32_t));
+    c.vals = dmalloc((size_t)(c.nnz > 0 ? c.nnz : 1) * ts);
+    GRB_TYPE_SWITCH(v->type->code, T,
+        GRB_LAUNCH("vec_compact", k_vec_compact<T>, nblk(n), 256, 0, v->present, (const T *)v->vals, pos, n,
+                   (uint32_t *)nullptr, (T *)c.vals));
+    return c;
+}
+__global__ void k_row_ptr2(int64_t *rowptr, int64_t nnz) { rowptr[0] = 0; rowptr[1] = nnz; }
+Csr vec_as_csr_row(GB_Object *v) {
+    int64_t n = v->nrows;
+    size_t ts = v->type->size;
+    Csr c;
+    c.nrows = 1; c.ncols = n;
+    int64_t *pos = present_scan(v->present, n);
+    c.nnz = read_i64(pos + n);
+    c.rowptr = dalloc<int64_t>(2);
+    GRB_LAUNCH("row_ptr2", k_row_ptr2, 1, 1, 0, c.rowptr, c.nnz);
+    c.colidx = dalloc<uint32_t>(c.nnz);
+    c.vals = dmalloc((size_t)(c.nnz > 0 ? c.nnz : 1) * ts);
+    GRB_TYPE_SWITCH(v->type->code, T,
+        GRB_LAUNCH("vec_compact", k_vec_compact<T>, nblk(n), 256, 0, v->present, (const T *)v->vals, pos, n,
+                   c.colidx, (T *)c.vals));
+    dfree(pos);
+    return c;
+}
+template <class T>
+__global__ void k_csr_col_to_vec(const int64_t *rowptr, const T *cv, int iso, int64_t n, T *vals, uint8_t *present) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int64_t a = rowptr[i], b = rowptr[i + 1];
+    present[i] = b > a;
+    if (b > a) vals[i] = cv[iso ? 0 : a];
+}
+template <class T>
+__global__ void k_csr_row_to_vec(const uint32_t *col, const T *cv, int iso, int64_t nnz, T *vals, uint8_t *present) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= nnz) return;
+    present[col[k]] = 1;
+    vals[col[k]] = cv[iso ? 0 : k];
+}
+// c must already hold values of v's type
+void csr_to_vec(const Csr &c, GB_Object *v, bool as_column) {
+    int64_t n = v->nrows;
+    GRB_TYPE_SWITCH(v->type->code, T, {
+        if (as_column) {
+            GRB_LAUNCH("csr_col_to_vec", k_csr_col_to_vec<T>, nblk(n), 256, 0, c.rowptr, (const T *)c.vals,
+                       (int)c.iso, n, (T *)v->vals, v->present);
+        } else {
+            dzero(v->present, (size_t)n);
+            if (c.nnz) GRB_LAUNCH("csr_row_to_vec", k_csr_row_to_vec<T>, nblk(c.nnz), 256, 0, c.colidx,
+                                  (const T *)c.vals, (int)c.iso, c.nnz, (T *)v->vals, v->present);
+        }
+    });
+    v->nvals = c.nnz; v->nvals_known = true; v->list_valid = false;
+}
+
+// ---------------------------------------------------------------- value casts (C typecast rules)
+template <class S, class D>
+__global__ void k_cast(const S *in, int64_t n, D *out) {
+    int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    if constexpr (std::is_same<D, bool>::value) out[k] = in[k] != (S)0;
+    else out[k] = (D)in[k];
+}
+void cast_array(const void *in, int from_code, void *out, int to_code, int64_t n) {
+    if (n == 0) return;
+    GRB_TYPE_SWITCH(from_code, S, {
+        GRB_TYPE_SWITCH(to_code, D, {
+            auto kern = k_cast<S, D>;
+            GRB_LAUNCH("cast", kern, nblk(n), 256, 0, (const S *)in, n, (D *)out);
+        });
+    });
+}
+void csr_cast_values(Csr &c, int from_code, int to_code) {
+    if (from_code == to_code) return;
+    int64_t n = c.iso ? 1 : c.nnz;
+    void *nv = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[to_code]);
+    cast_array(c.vals, from_code, nv, to_code, n);
+    dfree(c.vals);
+    c.vals = nv;
+}
