@@ -1,0 +1,373 @@
+// grb_ewise.cu — the loop-body operations that sit between the products in BFS / PageRank / SSSP / FastSV
+// (SURVEY 8f rank 1): masked scalar / vector assign, eWiseMult / eWiseAdd, apply(bind-2nd), reduce.
+// All of them are single-pass, bandwidth-trivial kernels over the dense vector layout and share the
+// product kernels' write-back (grb_spmv.cuh: epi_store), so vectors never leave HBM between products.
+// Reference call sites: graphblas/core/vector.py:1012-1140 (ewise), :1308 (apply), :1561 (reduce), :1772-1950 (assign).
+#define HAVE_EWISE 1
+#include "grb_internal.cuh"
+#include "grb_abi_lists.inc"
+#include "grb_ops.cuh"
+#include "grb_spmv.cuh"
+#include "grb_storage.cuh"
+
+static inline int nblk(int64_t n, int b = 256) { return (int)cdiv(n > 0 ? n : 1, b); }
+
+template <class T>
+static EpiArgs<T> epi_for(GB_Object *w, GB_Object *mask, const DescFlags &f, int accum) {
+    EpiArgs<T> e;
+    e.w_in = (const T *)w->vals; e.wp_in = w->present; e.w_out = (T *)w->vals; e.wp_out = w->present;
+    e.mask_p = mask ? mask->present : nullptr;
+    e.mask_v = mask ? mask->vals : nullptr;
+    e.mask_vsize = (mask && !f.structure) ? (int)mask->type->size : 0;
+    e.mask_fp = mask ? (mask->type->code == TC_FP32 || mask->type->code == TC_FP64) : 0;
+    e.comp = f.comp; e.replace = f.replace; e.accum = accum;
+    e.count = (unsigned long long *)w->d_nvals;
+    return e;
+}
+
+static int accum_code(const GrB_BinaryOp accum) {
+    if (!accum) return -1;
+    if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+    return accum->op;
+}
+
+static void check_vec(GB_Object *o, const char *what) {
+    if (o->kind == K_MATRIX) grb_throw(GrB_INVALID_OBJECT, std::string(what) + " must be a vector");
+}
+
+// w<m,replace> = accum(w, t) where t (values of type tcode + presence) is cast to w's type if needed
+static void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f, int accum, const void *t, int tcode,
+                              const uint8_t *tp) {
+    int64_t n = w->nrows;
+    int wcode = w->type->code;
+    void *tc = nullptr;
+    if (tcode != wcode) {
+        tc = dmalloc((size_t)(n > 0 ? n : 1) * w->type->size);
+        cast_array(t, tcode, tc, wcode, n);
+        t = tc;
+    }
+    dzero(w->d_nvals, sizeof(int64_t));
+    GRB_TYPE_SWITCH(wcode, W, {
+        EpiArgs<W> e = epi_for<W>(w, mask, f, accum);
+        GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, nblk(n), 256, 0, e, (const W *)t, tp, n);
+    });
+    dfree(tc);
+    vec_set_unknown_nvals(w);
+}
+
+// ---------------------------------------------------------------- assign
+template <class T>
+__global__ void __launch_bounds__(256) k_assign_scalar(EpiArgs<T> e, T x, int64_t n) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int c = 0;
+    if (i < n) c = epi_store(e, i, epi_allowed(e, i), true, x);
+    block_count_add(e.count, c);
+}
+// w(I)<m> = accum(w(I), x) for an explicit index list: positions outside I are left alone
+template <class T>
+__global__ void k_assign_scalar_list(EpiArgs<T> e, T x, const uint64_t *I, int64_t ni, int64_t n, int *bad) {
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= ni) return;
+    uint64_t i = I[k];
+    if (i >= (uint64_t)n) { *bad = 1; return; }
+    epi_store(e, (int64_t)i, epi_allowed(e, (int64_t)i), true, x);
+}
+
+template <class T>
+static GrB_Info vector_assign_scalar(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, T x, int xcode,
+                                     const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc) {
+    API_BEGIN
+    require_init();
+    GB_Object *w = obj_check(w_, "w");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    check_vec(w, "w");
+    if (mask) { check_vec(mask, "mask"); if (mask->nrows != w->nrows) grb_throw(GrB_DIMENSION_MISMATCH, "mask size differs from w"); }
+    DescFlags f = desc_flags(desc);
+    int acc = accum_code(accum);
+    int64_t n = w->nrows;
+    // value in w's type
+    void *dx = dmalloc(16);
+    h2d(dx, &x, sizeof(T));
+    void *dxc = dmalloc(16);
+    cast_array(dx, xcode, dxc, w->type->code, 1);
+    char hx[8];
+    d2h(hx, dxc, w->type->size);
+    stream_sync();
+    dfree(dx); dfree(dxc);
+    const bool all = (I == GrB_ALL);
+    GRB_TYPE_SWITCH(w->type->code, W, {
+        W xv; memcpy(&xv, hx, sizeof(W));
+        EpiArgs<W> e = epi_for<W>(w, mask, f, acc);
+        if (all) {
+            dzero(w->d_nvals, sizeof(int64_t));
+            GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, nblk(n), 256, 0, e, xv, n);
+            vec_set_unknown_nvals(w);
+        } else {
+            if (f.replace) grb_throw(GrB_NOT_IMPLEMENTED, "assign with an index list and replace");
+            if (!I && ni) grb_throw(GrB_NULL_POINTER, "I is NULL");
+            uint64_t *dI = dalloc<uint64_t>((int64_t)ni);
+            h2d(dI, I, (size_t)ni * 8);
+            int *dflag = (int *)g.d_scratch;
+            dzero(dflag, sizeof(int));
+            if (ni) GRB_LAUNCH("assign_scalar_list", k_assign_scalar_list<W>, nblk((int64_t)ni), 256, 0, e, xv, dI, (int64_t)ni, n, dflag);
+            int bad = 0;
+            d2h(&bad, dflag, sizeof(int));
+            stream_sync();
+            dfree(dI);
+            if (bad) grb_throw(GrB_INDEX_OUT_OF_BOUNDS, "assign index out of bounds");
+            count_present(w->present, n, w->d_nvals);
+            vec_set_unknown_nvals(w);
+        }
+    });
+    API_END(w_)
+}
+
+// ---------------------------------------------------------------- eWise
+template <class T, bool UNION, bool CMP>
+__global__ void __launch_bounds__(256) k_ewise(const T *u, const uint8_t *up, const T *v, const uint8_t *vp, int op,
+                                               void *t_, uint8_t *tp, int64_t n) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const bool a = up[i] != 0, b = vp[i] != 0;
+    bool has = UNION ? (a || b) : (a && b);
+    tp[i] = has;
+    if (!has) return;
+    if (CMP) {
+        bool *t = (bool *)t_;
+        t[i] = (a && b) ? cmp_rt<T>(op, u[i], v[i]) : (a ? (u[i] != (T)0) : (v[i] != (T)0));
+    } else {
+        T *t = (T *)t_;
+        t[i] = (a && b) ? binop_rt<T>(op, u[i], v[i]) : (a ? u[i] : v[i]);
+    }
+}
+
+static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_BinaryOp op,
+                         const GrB_Vector u_, const GrB_Vector v_, const GrB_Descriptor desc, bool is_union) {
+    require_init();
+    GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u"), *v = obj_check(v_, "v");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    if (!op) grb_throw(GrB_NULL_POINTER, "op is NULL");
+    check_vec(w, "w"); check_vec(u, "u"); check_vec(v, "v");
+    int64_t n = w->nrows;
+    if (u->nrows != n || v->nrows != n || (mask && mask->nrows != n)) grb_throw(GrB_DIMENSION_MISMATCH, "eWise: sizes differ");
+    DescFlags f = desc_flags(desc);
+    int acc = accum_code(accum);
+    int xcode = op->xcode, zcode = op->zcode;
+    const bool cmp = op->op >= OP_EQ;
+    void *uc = nullptr, *vc = nullptr;
+    const void *uv = u->vals, *vv = v->vals;
+    if (u->type->code != xcode) { uc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(u->vals, u->type->code, uc, xcode, n); uv = uc; }
+    if (v->type->code != xcode) { vc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(v->vals, v->type->code, vc, xcode, n); vv = vc; }
+    void *t = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[zcode]);
+    uint8_t *tp = dalloc<uint8_t>(n);
+    GRB_TYPE_SWITCH(xcode, X, {
+        auto kern = cmp ? (is_union ? k_ewise<X, true, true> : k_ewise<X, false, true>)
+                        : (is_union ? k_ewise<X, true, false> : k_ewise<X, false, false>);
+        GRB_LAUNCH(is_union ? "ewise_add" : "ewise_mult", kern, nblk(n), 256, 0, (const X *)uv, u->present,
+                   (const X *)vv, v->present, op->op, t, tp, n);
+    });
+    vec_writeback_any(w, mask, f, acc, t, zcode, tp);
+    dfree(t); dfree(tp); dfree(uc); dfree(vc);
+}
+
+// ---------------------------------------------------------------- apply bind-2nd
+template <class T, bool CMP>
+__global__ void __launch_bounds__(256) k_apply2nd(const T *u, const uint8_t *up, T y, int op, void *t_, uint8_t *tp, int64_t n) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const bool a = up[i] != 0;
+    tp[i] = a;
+    if (!a) return;
+    if (CMP) ((bool *)t_)[i] = cmp_rt<T>(op, u[i], y);
+    else ((T *)t_)[i] = binop_rt<T>(op, u[i], y);
+}
+
+template <class T>
+static GrB_Info vector_apply2nd(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_BinaryOp op,
+                                const GrB_Vector u_, T y, int ycode, const GrB_Descriptor desc) {
+    API_BEGIN
+    require_init();
+    GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    if (!op) grb_throw(GrB_NULL_POINTER, "op is NULL");
+    check_vec(w, "w"); check_vec(u, "u");
+    int64_t n = w->nrows;
+    if (u->nrows != n || (mask && mask->nrows != n)) grb_throw(GrB_DIMENSION_MISMATCH, "apply: sizes differ");
+    DescFlags f = desc_flags(desc);
+    int acc = accum_code(accum);
+    int xcode = op->xcode, zcode = op->zcode;
+    const bool cmp = op->op >= OP_EQ;
+    void *uc = nullptr;
+    const void *uv = u->vals;
+    if (u->type->code != xcode) { uc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(u->vals, u->type->code, uc, xcode, n); uv = uc; }
+    void *t = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[zcode]);
+    uint8_t *tp = dalloc<uint8_t>(n);
+    GRB_TYPE_SWITCH(xcode, X, {
+        X yv = (X)y;
+        (void)ycode;
+        auto kern = cmp ? k_apply2nd<X, true> : k_apply2nd<X, false>;
+        GRB_LAUNCH("apply2nd", kern, nblk(n), 256, 0, (const X *)uv, u->present, yv, op->op, t, tp, n);
+    });
+    vec_writeback_any(w, mask, f, acc, t, zcode, tp);
+    dfree(t); dfree(tp); dfree(uc);
+    API_END(w_)
+}
+
+// ---------------------------------------------------------------- reduce to a C scalar
+template <class T>
+__global__ void __launch_bounds__(256) k_reduce(const T *vals, const uint8_t *present, int iso, int64_t n, int op,
+                                                T *partial, uint8_t *partial_has) {
+    __shared__ T s_v[8];
+    __shared__ uint8_t s_h[8];
+    T acc = (T)0; bool has = false;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (present && !present[i]) continue;
+        T x = vals[iso ? 0 : i];
+        acc = has ? binop_rt<T>(op, acc, x) : x; has = true;
+    }
+    for (int o = 16; o; o >>= 1) {
+        T oa = __shfl_xor_sync(0xffffffffu, acc, o);
+        bool oh = __shfl_xor_sync(0xffffffffu, (int)has, o) != 0;
+        if (oh) { acc = has ? binop_rt<T>(op, acc, oa) : oa; has = true; }
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { s_v[warp] = acc; s_h[warp] = has; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        T a = (T)0; bool h = false;
+        for (int k = 0; k < (int)(blockDim.x >> 5); k++)
+            if (s_h[k]) { a = h ? binop_rt<T>(op, a, s_v[k]) : s_v[k]; h = true; }
+        partial[blockIdx.x] = a; partial_has[blockIdx.x] = h;
+    }
+}
+
+// reduce (vals[n], optional presence) with a monoid; returns has + value (in T) on the host
+template <class T>
+static bool reduce_device(const T *vals, const uint8_t *present, bool iso, int64_t n, int op, T *out) {
+    if (n == 0) return false;
+    int blocks = (int)(cdiv(n, 256) < 1184 ? cdiv(n, 256) : 1184);
+    T *p1 = dalloc<T>(blocks + 1);
+    uint8_t *h1 = dalloc<uint8_t>(blocks + 1);
+    GRB_LAUNCH("reduce", k_reduce<T>, blocks, 256, 0, vals, present, (int)iso, n, op, p1, h1);
+    GRB_LAUNCH("reduce_final", k_reduce<T>, 1, 256, 0, (const T *)p1, (const uint8_t *)h1, 0, (int64_t)blocks, op, p1 + blocks, h1 + blocks);
+    T hv; uint8_t hh = 0;
+    d2h(&hv, p1 + blocks, sizeof(T));
+    d2h(&hh, h1 + blocks, 1);
+    stream_sync();
+    dfree(p1); dfree(h1);
+    *out = hv;
+    return hh != 0;
+}
+
+// times/plus over an iso matrix would need nnz repetitions: expand the count analytically only for idempotent ops
+template <class T>
+static GrB_Info reduce_to_scalar(T *c, const GrB_BinaryOp accum, const GrB_Monoid monoid, GB_Object *A, int ccode) {
+    if (!c) grb_throw(GrB_NULL_POINTER, "c is NULL");
+    if (!monoid) grb_throw(GrB_NULL_POINTER, "monoid is NULL");
+    int mcode = monoid->tcode;
+    const void *vals; const uint8_t *present; int64_t n; bool iso = false; int vcode = A->type->code;
+    if (A->kind == K_MATRIX) { vals = A->csr.vals; present = nullptr; n = A->csr.nnz; iso = A->csr.iso; }
+    else { vals = A->vals; present = A->present; n = A->nrows; }
+    void *vc = nullptr;
+    if (vcode != mcode) {
+        int64_t m = iso ? 1 : n;
+        vc = dmalloc((size_t)(m > 0 ? m : 1) * kTypeSize[mcode]);
+        cast_array(vals, vcode, vc, mcode, m);
+        vals = vc;
+    }
+    bool has = false;
+    double as_double = 0; int64_t as_i64 = 0; uint64_t as_u64 = 0;
+    GRB_TYPE_SWITCH(mcode, M, {
+        M r = (M)0;
+        has = reduce_device<M>((const M *)vals, present, iso, n, monoid->op, &r);
+        as_double = (double)r; as_i64 = (int64_t)r; as_u64 = (uint64_t)r;
+    });
+    dfree(vc);
+    if (has) {
+        T r;
+        if (mcode == TC_FP32 || mcode == TC_FP64) r = (T)as_double;
+        else if (mcode == TC_UINT64) r = (T)as_u64;
+        else r = (T)as_i64;
+        if (accum) {
+            if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+            *c = binop_rt<T>(accum->op, *c, r);
+        } else *c = r;
+    } else if (!accum) {
+        // empty input: the monoid identity (C API: reduce of nothing yields the identity)
+        GRB_TYPE_SWITCH(ccode, C, {
+            C idv = (C)0;
+            switch (monoid->op) {
+            case OP_MIN: if constexpr (std::is_same<C, bool>::value) idv = true;
+                         else if constexpr (std::is_floating_point<C>::value) idv = std::numeric_limits<C>::infinity();
+                         else idv = std::numeric_limits<C>::max(); break;
+            case OP_MAX: if constexpr (std::is_same<C, bool>::value) idv = false;
+                         else if constexpr (std::is_floating_point<C>::value) idv = -std::numeric_limits<C>::infinity();
+                         else idv = std::numeric_limits<C>::lowest(); break;
+            case OP_TIMES: case OP_LAND: case OP_LXNOR: idv = (C)1; break;
+            default: idv = (C)0;
+            }
+            *c = (T)idv;
+        });
+    }
+    return GrB_SUCCESS;
+}
+
+extern "C" {
+
+GrB_Info GrB_Vector_eWiseMult_BinaryOp(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
+                                       const GrB_BinaryOp op, const GrB_Vector u, const GrB_Vector v,
+                                       const GrB_Descriptor desc) {
+    API_BEGIN
+    vector_ewise(w, mask, accum, op, u, v, desc, false);
+    API_END(w)
+}
+GrB_Info GrB_Vector_eWiseAdd_BinaryOp(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
+                                      const GrB_BinaryOp op, const GrB_Vector u, const GrB_Vector v,
+                                      const GrB_Descriptor desc) {
+    API_BEGIN
+    vector_ewise(w, mask, accum, op, u, v, desc, true);
+    API_END(w)
+}
+GrB_Info GrB_Vector_assign(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_Vector u_,
+                           const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc) {
+    (void)ni;
+    API_BEGIN
+    require_init();
+    GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    check_vec(w, "w"); check_vec(u, "u");
+    if (I != GrB_ALL) grb_throw(GrB_NOT_IMPLEMENTED, "vector assign supports GrB_ALL only");
+    if (u->nrows != w->nrows || (mask && mask->nrows != w->nrows)) grb_throw(GrB_DIMENSION_MISMATCH, "assign: sizes differ");
+    vec_writeback_any(w, mask, desc_flags(desc), accum_code(accum), u->vals, u->type->code, u->present);
+    API_END(w_)
+}
+
+#define DEF_EWISE_TYPED(NAME, CT, CODE)                                                                              \
+    GrB_Info GrB_Vector_assign_##NAME(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, CT x,          \
+                                      const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc) {               \
+        return vector_assign_scalar<CT>(w, mask, accum, x, CODE, I, ni, desc);                                      \
+    }                                                                                                               \
+    GrB_Info GrB_Vector_apply_BinaryOp2nd_##NAME(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,     \
+                                                 const GrB_BinaryOp op, const GrB_Vector u, CT y,                   \
+                                                 const GrB_Descriptor desc) {                                       \
+        return vector_apply2nd<CT>(w, mask, accum, op, u, y, CODE, desc);                                           \
+    }                                                                                                               \
+    GrB_Info GrB_Vector_reduce_##NAME(CT *c, const GrB_BinaryOp accum, const GrB_Monoid monoid, const GrB_Vector u, \
+                                      const GrB_Descriptor desc) {                                                  \
+        (void)desc;                                                                                                 \
+        API_BEGIN                                                                                                   \
+        require_init();                                                                                             \
+        return reduce_to_scalar<CT>(c, accum, monoid, obj_check(u, "u"), CODE);                                     \
+        API_END(u)                                                                                                  \
+    }                                                                                                               \
+    GrB_Info GrB_Matrix_reduce_##NAME(CT *c, const GrB_BinaryOp accum, const GrB_Monoid monoid, const GrB_Matrix A, \
+                                      const GrB_Descriptor desc) {                                                  \
+        (void)desc;                                                                                                 \
+        API_BEGIN                                                                                                   \
+        require_init();                                                                                             \
+        return reduce_to_scalar<CT>(c, accum, monoid, obj_check(A, "A"), CODE);                                     \
+        API_END(A)                                                                                                  \
+    }
+GRB_TYPE_LIST(DEF_EWISE_TYPED)
+
+}  // extern "C"

@@ -171,6 +171,9 @@ Csr vec_as_csr_row(GB_Object *v);                         // 1 x n
 void csr_to_vec(const Csr &c, GB_Object *v, bool as_column);
 void csr_cast_values(Csr &c, int from_code, int to_code);
 
+struct DescFlags { bool replace, comp, structure, tran0, tran1; int axb; };
+DescFlags desc_flags(const GrB_Descriptor d);
+
 // API boundary: catch GrbError, stash the message on the first object for GrB_*_error
 #define API_BEGIN try {
 #define API_END(errobj)                                                          \

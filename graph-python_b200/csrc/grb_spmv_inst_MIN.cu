@@ -1,0 +1,14 @@
+// semiring kernels with the MIN monoid (instantiated at build time; see grb_spmv.cuh)
+#include "grb_spmv_inst.inc"
+bool spmv_pull_MIN(int mul, int tcode, const void *pa, int mode) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_pull_t<Semiring<OP_MIN, OP_##MUL, CT_##TYPE>>(pa, mode); return true; }
+    GRB_SEMIRINGS_OF_MIN(X)
+#undef X
+    return false;
+}
+bool spmv_push_MIN(int mul, int tcode, const void *pa) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_push_t<Semiring<OP_MIN, OP_##MUL, CT_##TYPE>>(pa); return true; }
+    GRB_SEMIRINGS_OF_MIN(X)
+#undef X
+    return false;
+}

@@ -1,0 +1,191 @@
+"""GPU: GrB_mxv / GrB_vxm through the C-ABI vs the CPU oracle on seeded inputs — every kernel path
+(streaming pull, early-exit pull, push), masks, accumulators, replace, transposes, types.
+Bit-exact for integer / boolean semirings; 1e-5 relative for fp plus_times (north_star tolerance)."""
+import numpy as np
+import pytest
+
+from gb_util import to_gpu_matrix, to_gpu_vector, vec_equal
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+FP_TOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def gb():
+    import graphblas_b200 as gb
+
+    gb.init("b200")
+    yield gb
+    gb.set_option("force_direction", 0)
+
+
+def _rand_vec(rng, n, dtype, density):
+    p = (rng.random(n) < density).astype(np.uint8)
+    if dtype.startswith("FP"):
+        v = rng.random(n).astype(O.NP_TYPES[dtype])
+    elif dtype == "BOOL":
+        v = rng.random(n) < 0.7
+    else:
+        v = rng.integers(0 if dtype.startswith("U") else -50, 100, size=n).astype(O.NP_TYPES[dtype])
+    return O.Vec(v, p, dtype)
+
+
+def _sr(gb, mon, mul):
+    from graphblas_b200 import semiring
+
+    return getattr(semiring, f"{mon.lower()}_{mul.lower()}")
+
+
+CASES = [
+    ("PLUS", "TIMES", "INT64"), ("PLUS", "TIMES", "FP32"), ("PLUS", "TIMES", "FP64"), ("PLUS", "SECOND", "FP32"),
+    ("PLUS", "PAIR", "INT64"), ("PLUS", "FIRST", "INT32"), ("MIN", "PLUS", "INT64"), ("MIN", "PLUS", "FP64"),
+    ("MIN", "FIRST", "UINT64"), ("MIN", "SECOND", "UINT32"), ("MAX", "PLUS", "INT32"), ("MAX", "MIN", "FP32"),
+    ("ANY", "PAIR", "BOOL"), ("ANY", "PAIR", "INT32"), ("LOR", "LAND", "BOOL"), ("LXOR", "LAND", "BOOL"),
+    ("MIN", "TIMES", "UINT32"), ("PLUS", "MIN", "INT64"),
+]
+
+
+@pytest.mark.parametrize("mon,mul,dt", CASES)
+@pytest.mark.parametrize("direction", [1, 2])   # 1 = forced pull, 2 = forced push
+def test_products_vs_oracle_rmat(gb, mon, mul, dt, direction):
+    rng = np.random.default_rng(hash((mon, mul, dt)) % 2**31)
+    scale = 11
+    n = 1 << scale
+    vm = 2 if dt.startswith("FP") else (0 if dt == "BOOL" else 1)
+    A = O.rmat_matrix(scale, dt, value_mode=vm)
+    gA = to_gpu_matrix(gb, A)
+    At = A.transpose()
+    tol = FP_TOL if (dt.startswith("FP") and mon == "PLUS") else None
+    gb.set_option("force_direction", direction)
+    sr = _sr(gb, mon, mul)
+    for density in (1.0, 0.3, 0.004):
+        u = _rand_vec(rng, n, dt, density)
+        gu = to_gpu_vector(gb, u)
+        # mxv, vxm, and their transposed forms
+        for kind, tran in (("mxv", False), ("mxv", True), ("vxm", False), ("vxm", True)):
+            w = O.Vec.empty(n, dt)
+            if kind == "mxv":
+                O.mxv(w, A, u, mon, mul, dt, tran0=tran, At=At)
+                gw = ((gA.T if tran else gA).mxv(gu, sr)).new()
+            else:
+                O.vxm(w, u, A, mon, mul, dt, tran1=tran, At=At)
+                gw = (gu.vxm(gA.T if tran else gA, sr)).new()
+            if mon == "ANY" and mul != "PAIR":
+                assert np.array_equal(gw.to_dense()[1], w.present.astype(bool))
+            else:
+                assert vec_equal(gw, w, tol), (kind, tran, density, gb.last_kernel())
+            assert gw.nvals == w.nvals
+
+
+@pytest.mark.parametrize("direction", [1, 2])
+@pytest.mark.parametrize("accum", [None, "PLUS", "MIN"])
+@pytest.mark.parametrize("replace", [False, True])
+@pytest.mark.parametrize("comp", [False, True])
+@pytest.mark.parametrize("structure", [False, True])
+def test_writeback_semantics_vs_oracle(gb, direction, accum, replace, comp, structure):
+    """C API 2.0 write-back: every mask kind x accum x replace, fused epilogue (pull) and dense write-back (push)."""
+    from graphblas_b200 import binary, semiring
+
+    rng = np.random.default_rng(7)
+    n = 3000
+    dt = "INT64"
+    A = O.rmat_matrix(11, dt, value_mode=1)
+    A = O.Mat(A.indptr[: n + 1], A.indices[: A.indptr[n]] % n, A.values[: A.indptr[n]], (n, n), dt)
+    A = O.Mat.from_coo(*_dedup(A), n, n, dt)
+    gA = to_gpu_matrix(gb, A)
+    gb.set_option("force_direction", direction)
+    u = _rand_vec(rng, n, dt, 0.2)
+    w0 = _rand_vec(rng, n, dt, 0.5)
+    m = _rand_vec(rng, n, "INT32", 0.5)
+    m.values[rng.random(n) < 0.5] = 0          # stored zeros: false under a value mask, true structurally
+    w = w0.dup()
+    O.mxv(w, A, u, "MIN", "PLUS", dt, mask=m, accum=accum, replace=replace, comp=comp, structure=structure)
+    gw, gm = to_gpu_vector(gb, w0), to_gpu_vector(gb, m)
+    mask = gm.S if structure else gm.V
+    mask = ~mask if comp else mask
+    kw = dict(mask=mask, replace=replace)
+    if accum:
+        kw["accum"] = getattr(binary, accum.lower())
+    gw(**kw) << gA.mxv(to_gpu_vector(gb, u), semiring.min_plus)
+    assert vec_equal(gw, w)
+    assert gw.nvals == w.nvals
+
+
+def _dedup(A):
+    r, c, v = A.to_coo()
+    keys = r * A.shape[1] + c
+    _, first = np.unique(keys, return_index=True)
+    return r[first], c[first], v[first]
+
+
+def test_aliased_output_pingpong(gb):
+    """w(min) << w.vxm(A, min_plus): the output aliases the input; Bellman-Ford to a fixed point vs scipy."""
+    import scipy.sparse as sp
+    from scipy.sparse.csgraph import bellman_ford
+
+    from graphblas_b200 import binary, semiring
+
+    scale = 10
+    n = 1 << scale
+    A = O.rmat_matrix(scale, "INT64", value_mode=1)
+    gA = to_gpu_matrix(gb, A)
+    gb.set_option("force_direction", 0)
+    src = int(np.argmax(np.diff(A.indptr)))
+    gw = gb.Vector.from_coo([src], [0], dtype="INT64", size=n)
+    for _ in range(n):
+        before = gw.dup()
+        gw(binary.min) << gw.vxm(gA, semiring.min_plus)
+        if gw.isequal(before):
+            break
+    dist = bellman_ford(sp.csr_matrix((A.values.astype(np.float64), A.indices, A.indptr), shape=A.shape),
+                        indices=src, directed=True)
+    vals, pres = gw.to_dense()
+    assert np.array_equal(pres, np.isfinite(dist))
+    assert np.array_equal(vals[pres], dist[pres].astype(np.int64))
+
+
+def test_level_bfs_direction_optimising(gb):
+    """Level BFS (reference notebooks/Example B.1 cell 8): q(~v.S, replace) << q.vxm(A, any_pair); levels
+    must match scipy's BFS order distances, with the push / early-exit pull switch left on auto."""
+    import scipy.sparse as sp
+    from scipy.sparse.csgraph import shortest_path
+
+    from graphblas_b200 import semiring
+
+    scale = 12
+    n = 1 << scale
+    A = O.rmat_matrix(scale, "BOOL", symmetrize=True)
+    gA = to_gpu_matrix(gb, A)
+    gb.set_option("force_direction", 0)
+    src = int(np.argmax(np.diff(A.indptr)))
+    q = gb.Vector.from_coo([src], [True], dtype="BOOL", size=n)
+    v = gb.Vector("INT32", n)
+    level, kernels = 0, set()
+    while q.nvals:
+        v(q.S)[:] = level
+        q(~v.S, replace=True) << q.vxm(gA, semiring.any_pair)
+        kernels.add(gb.last_kernel())
+        level += 1
+    d = shortest_path(sp.csr_matrix((np.ones(A.nnz), A.indices, A.indptr), shape=A.shape), method="D",
+                      unweighted=True, indices=src)
+    vals, pres = v.to_dense()
+    assert np.array_equal(pres, np.isfinite(d))
+    assert np.array_equal(vals[pres], d[pres].astype(np.int32))
+
+
+def test_type_mismatch_is_cast_like_c(gb):
+    """Operands of other types are typecast to the semiring's type; output of another type is cast on write-back."""
+    from graphblas_b200 import semiring
+
+    rng = np.random.default_rng(3)
+    n = 500
+    A = O.rmat_matrix(9, "INT32", value_mode=1)
+    A = O.Mat(A.indptr[: n + 1], A.indices[: A.indptr[n]], A.values[: A.indptr[n]], (n, 512), "INT32")
+    u = _rand_vec(rng, 512, "FP64", 0.5)
+    gw = gb.Vector("FP32", n)
+    gw << to_gpu_matrix(gb, A).mxv(to_gpu_vector(gb, u), semiring.plus_times["FP64"])
+    w = O.Vec.empty(n, "FP32")
+    t = O.spmv(A, u, "PLUS", "TIMES", "FP64")
+    O.vec_writeback(w, t)
+    assert vec_equal(gw, w, 1e-6)
