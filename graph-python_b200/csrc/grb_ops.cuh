@@ -244,3 +244,19 @@ template <int MON, int MUL, class T> struct Semiring {
     static constexpr bool kUsesY = !(MUL == OP_FIRST || MUL == OP_ONEB);   // second operand's value
     static HD T mult(T x, T y) { return BinOp<MUL, T>::apply(x, y); }
 };
+
+// run-time monoid identity (host side: pre-filling dense accumulators)
+template <class T> inline T monoid_identity_rt(int mon) {
+    switch (mon) {
+    case OP_MIN:
+        if constexpr (std::is_same<T, bool>::value) return true;
+        else if constexpr (std::is_floating_point<T>::value) return std::numeric_limits<T>::infinity();
+        else return std::numeric_limits<T>::max();
+    case OP_MAX:
+        if constexpr (std::is_same<T, bool>::value) return false;
+        else if constexpr (std::is_floating_point<T>::value) return -std::numeric_limits<T>::infinity();
+        else return std::numeric_limits<T>::lowest();
+    case OP_LAND: case OP_LXNOR: case OP_TIMES: return (T)1;
+    default: return (T)0;
+    }
+}

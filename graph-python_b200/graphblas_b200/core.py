@@ -64,11 +64,12 @@ _VALID_OPTS = ("axb_method", "nthreads", "chunk", "sort", "secure_import", "comp
 
 
 class _Handle:
-    __slots__ = ("_carg", "_keep")
+    __slots__ = ("_carg", "_keep", "return_type")
 
-    def __init__(self, carg, keep=None):
+    def __init__(self, carg, keep=None, return_type=None):
         self._carg = carg
         self._keep = keep
+        self.return_type = return_type
 
 
 def _custom_descriptor(replace_, comp, structure, t0, t1, opts):
@@ -850,6 +851,26 @@ class Matrix(BaseType):
             raise errors.error_for(info)("GrB_Matrix_import")
         return cls._wrap(gb_obj, dt, nrows, ncols, name)
 
+    @classmethod
+    def rmat(cls, scale, dtype=dtypes.BOOL, *, edgefactor=16, seed=None, symmetrize=False, value_mode=0, name=None):
+        """Graph500-style R-MAT graph generated in HBM (bench utility): bit-identical to
+        oracle.rmat_matrix(scale, dtype, edgefactor, seed, symmetrize, value_mode)."""
+        dt = lookup_dtype(dtype)
+        seed = 42 + scale if seed is None else seed
+        gb_obj = ffi.new("GrB_Matrix*")
+        info = lib.GxB_b200_Matrix_rmat(gb_obj, dt._carg, int(scale), int(edgefactor), int(seed), int(bool(symmetrize)),
+                                        int(value_mode))
+        if info != lib.GrB_SUCCESS:
+            raise errors.error_for(info)("GxB_b200_Matrix_rmat")
+        n = 1 << scale
+        return cls._wrap(gb_obj, dt, n, n, name)
+
+    def rowblock(self, row_begin, row_end, *, name=None):
+        """Rows [row_begin, row_end) as a new matrix: the 1-D row-block shard of SURVEY 8e."""
+        gb_obj = ffi.new("GrB_Matrix*")
+        call("GxB_b200_Matrix_rowblock", [gb_obj, self, int(row_begin), int(row_end)])
+        return Matrix._wrap(gb_obj, self.dtype, int(row_end) - int(row_begin), self._ncols, name)
+
     def to_coo(self, dtype=None, *, rows=True, columns=True, values=True, sort=True):
         n = self.nvals
         dt = lookup_dtype(dtype) if dtype is not None else self.dtype
@@ -975,7 +996,7 @@ class Matrix(BaseType):
     def select(self, which, thunk=0):
         """tril / triu / diag / offdiag (builds the triangle-count operand L on the device)."""
         opname = {"tril": "GrB_TRIL", "triu": "GrB_TRIU", "diag": "GrB_DIAG", "offdiag": "GrB_OFFDIAG"}[which]
-        return Expression("select", "GrB_Matrix_select_INT64", [self], _Handle(getattr(lib, opname)), Matrix, self.shape,
+        return Expression("select", "GrB_Matrix_select_INT64", [self], _Handle(getattr(lib, opname), return_type=self.dtype), Matrix, self.shape,
                           scalar_args=(int(thunk),), at=self._is_transposed)
 
     def ewise_mult(self, other, op=binary.times):
