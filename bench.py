@@ -1,0 +1,471 @@
+#!/usr/bin/env python
+"""bench.py — headline measurement of libgrb_b200's hot path (BASELINE.json configs[1]):
+
+    PageRank, 20 iterations of  r(plus) << A.T.mxv(w, semiring.plus_times)  in FP32 on an R-MAT graph
+    (scale 22, edge factor 16 per GPU), loop-body ops included, through the reference-shaped API.
+
+One JSON line on stdout (rank 0).  `value` = GTEPS with the graph resident in HBM (CUDA events, max over ranks);
+`e2e` = the same metric through the public API from pinned HOST buffers (CSC import + vector import + 20
+iterations + result export inside the timed region); `roofline` = spmv_pull's algorithmic bytes / its measured
+launch time against MEASURED_PEAKS.json; `cpu_baseline` = the OpenMP oracle port on this box's host cores on a
+bounded sample.  `--impl reference` times that CPU port alone on the same config (python-graphblas's own engine,
+SuiteSparse:GraphBLAS, is a third-party library that is neither in /root/reference nor installed here).
+N > 1 (torchrun): weak scaling, scale 22 + log2(N); the pull matrix is sharded by 1-D row blocks, every
+iteration all-gathers the FP32 vector over NCCL.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "graph-python_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "GTEPS (masked mxv/vxm)"
+ITERS = 20
+DAMPING = 0.85
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scale", type=int, default=22, help="R-MAT scale per GPU (weak scaling adds log2(gpus))")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--breakdown", action="store_true", help="print per-kernel device times of the timed region to stderr")
+    ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# ---------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        try:
+            rows = [ln.split(",") for ln in open(self.path).read().strip().splitlines() if ln.strip()]
+            sm = [float(r[1]) for r in rows]
+            out["samples"] = len(sm)
+            if sm:
+                out["sm_mhz"] = float(np.median(sm))
+                out["sm_max_mhz"] = float(rows[0][2])
+                out["power_w_max"] = max(float(r[3]) for r in rows)
+                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+                for k, nm in enumerate(names):
+                    if any(r[5 + k].strip().lower().startswith("active") for r in rows):
+                        out["reasons"].append(nm)
+        except Exception as e:   # no nvidia-smi: report that instead of inventing clocks
+            out["error"] = str(e)
+        finally:
+            if self.path and os.path.exists(self.path):
+                os.unlink(self.path)
+        return out
+
+
+# ---------------------------------------------------------------------------------------------- host side (CPU port)
+def host_pull_graph(scale):
+    """P = A' (rows = destinations) of the R-MAT graph as an oracle Mat with FP32 values; bit-identical to what
+    the device generator builds (tests/test_gpu_matrix_parity.py::test_device_rmat_equals_oracle_rmat)."""
+    from oracle import oracle as O
+
+    src, dst = O.rmat_edges(scale)
+    n = np.uint64(1) << np.uint64(scale)
+    keep = src != dst
+    keys = np.unique(dst[keep] * n + src[keep])          # sorted by (dst, src): CSR of A'
+    rows, cols = (keys // n).astype(np.int64), (keys % n).astype(np.int64)
+    vals = O.edge_value(cols, rows, 2, "FP32")           # value belongs to the edge (src=cols, dst=rows) of A
+    indptr = np.zeros(int(n) + 1, dtype=np.int64)
+    indptr[1:] = np.cumsum(np.bincount(rows, minlength=int(n)))
+    outdeg = np.bincount(cols, minlength=int(n)).astype(np.float32)
+    return O.Mat(indptr, cols, vals, (int(n), int(n)), "FP32"), outdeg
+
+
+def cpu_pagerank(P, d, iters):
+    """The PageRank loop on the CPU port: w = r / d; r[:] = teleport; r(plus) << A.T.mxv(w, plus_times)."""
+    from oracle import oracle as O
+
+    n = P.shape[0]
+    teleport = np.float32((1 - DAMPING) / n)
+    ones = np.ones(n, dtype=np.uint8)
+    r = O.Vec(np.full(n, 1.0 / n, dtype=np.float32), ones, "FP32")
+    for _ in range(iters):
+        w = O.Vec(r.values / d, ones, "FP32")
+        r.values[:] = teleport
+        O.mxv(r, P, w, "PLUS", "TIMES", "FP32", accum="PLUS")
+    return r.values
+
+
+def degree_scaling(outdeg):
+    """d = outdeg / damping, with dangling vertices mapped to 1 so the division stays finite."""
+    d = outdeg.astype(np.float32) / np.float32(DAMPING)
+    d[d == 0] = 1.0
+    return d
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path on the host cores (oracle port, all threads)."""
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    from oracle import oracle as O
+
+    O.build()
+    job_scale = args.scale + int(np.log2(max(args.gpus, 1)))
+    scale = min(job_scale, 22)    # bounded sample: the host build of larger graphs alone takes minutes
+    P, outdeg = host_pull_graph(scale)
+    d = degree_scaling(outdeg)
+    nnz = P.nnz
+    for _ in range(max(args.warmup, 1)):
+        cpu_pagerank(P, d, 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_pagerank(P, d, ITERS)
+    dt = (time.perf_counter() - t0) / args.steps
+    gteps = ITERS * nnz / dt / 1e9
+    cores = O.num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gteps, "unit": "GTEPS", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(job_scale, nnz << (job_scale - scale), args.gpus),
+        "cpu_baseline": {"value": gteps, "unit": "GTEPS", "cores": cores, "kind": "port",
+                         "sample": f"{ITERS} PageRank iterations x {args.steps} steps on the scale-{scale} graph"
+                                   + ("" if scale == job_scale else f" (job config is scale {job_scale}; TEPS measured on the scale-{scale} sample)")},
+        "e2e": {"value": gteps, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "python-graphblas computes through SuiteSparse:GraphBLAS (not in /root/reference, not installed); "
+                "this arm is the OpenMP C restatement under oracle/ on all host threads",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(scale, nnz, gpus):
+    return {"workload": f"PageRank x{ITERS} iterations: r(plus) << A.T.mxv(w, plus_times) FP32, R-MAT scale {scale} "
+                        f"edgefactor 16 (BASELINE configs[1]; weak scaling: scale 22 + log2(gpus))",
+            "scale": scale, "nnz": int(nnz), "iterations": ITERS,
+            "parallelism": "1 GPU" if gpus == 1 else f"1-D row blocks over {gpus} GPUs + NCCL all-gather of w",
+            "l2": "inputs larger than L2 (matrix stream >= 0.8 GB per iteration vs 126 MB L2); no explicit flush"}
+
+
+# ---------------------------------------------------------------------------------------------- device side
+class _DevArray:
+    """Zero-copy torch view of a libgrb_b200 device buffer (for NCCL collectives and torch-side setup)."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 3}
+
+
+def dev_tensor(ptr, n, typestr):
+    import torch
+
+    return torch.as_tensor(_DevArray(ptr, n, typestr), device="cuda")
+
+
+def vector_tensor(gb, v, typestr="<f4"):
+    vals, pres = gb.ffi.new("void**"), gb.ffi.new("void**")
+    info = gb.lib.GxB_b200_Vector_device_ptrs(vals, pres, v._carg)
+    assert info == gb.lib.GrB_SUCCESS
+    return dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), v.size, typestr)
+
+
+def kernel_time(gb, name):
+    ms, cnt = gb.ffi.new("double*"), gb.ffi.new("uint64_t*")
+    gb.lib.GxB_b200_kernel_time(name.encode(), ms, cnt)
+    return float(ms[0]), int(cnt[0])
+
+
+class PageRankJob:
+    """Device-resident state of one rank: its row block of the pull matrix, the full-length w, and r / d blocks."""
+
+    def __init__(self, gb, scale, rank, world):
+        import torch
+        from graphblas_b200 import Matrix, Vector
+
+        self.gb, self.rank, self.world = gb, rank, world
+        n = 1 << scale
+        self.n = n
+        A = Matrix.rmat(scale, "FP32", value_mode=2)            # rows = sources; same graph on every rank
+        self.nnz_total = A.nvals
+        rp = gb.ffi.new("void**")
+        gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
+        rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+        outdeg = (rowptr[1:] - rowptr[:-1]).to(torch.float32)
+        d = outdeg / DAMPING
+        d[d == 0] = 1.0
+        self.lo, self.hi = rank * n // world, (rank + 1) * n // world
+        nb = self.hi - self.lo
+        if world == 1:
+            self.P, self.transposed = A, True                    # r(plus) << A.T.mxv(w): pull over the cached columns
+            gb.lib.GxB_b200_Matrix_prepare(A._carg, 1)
+        else:
+            AT = A.T.new()
+            self.P, self.transposed = AT.rowblock(self.lo, self.hi), False
+            del AT, A
+        self.nnz_local = self.P.nvals
+        self.d = Vector.from_dense(d[self.lo:self.hi].cpu().numpy())
+        self.r = Vector.from_dense(np.full(nb, 1.0 / n, dtype=np.float32))
+        self.wb = Vector.from_dense(np.zeros(nb, dtype=np.float32))
+        self.w = self.wb if world == 1 else Vector.from_dense(np.zeros(n, dtype=np.float32))
+        self.teleport = float(np.float32((1 - DAMPING) / n))
+        if world > 1:
+            self.wb_t, self.w_t = vector_tensor(gb, self.wb), vector_tensor(gb, self.w)
+        gb.sync()
+
+    def reset(self):
+        self.r[:] << 1.0 / self.n
+
+    def step(self):
+        """20 iterations, exactly the notebook's loop body around the product (reference notebooks/Pagerank Demo.ipynb
+        cell 9): w = r / d; r[:] = teleport; r(plus) << A.T.mxv(w, plus_times)."""
+        import torch.distributed as dist
+        from graphblas_b200 import binary, semiring
+
+        P = self.P.T if self.transposed else self.P
+        for _ in range(ITERS):
+            self.wb << self.r.ewise_mult(self.d, binary.truediv)
+            if self.world > 1:
+                dist.all_gather_into_tensor(self.w_t, self.wb_t)
+            self.r[:] << self.teleport
+            self.r(binary.plus) << P.mxv(self.w, semiring.plus_times)
+
+
+def e2e_pagerank(gb, host, pinned):
+    """The same 20 iterations from HOST buffers through the public API: import the graph by columns (CSC of A,
+    uint64 indices as the C ABI prescribes), import d and r, iterate, export r.  Returns (r_host, h2d, d2h)."""
+    from graphblas_b200 import Matrix, Vector, binary, semiring
+
+    indptr, indices, values, d, r0 = host
+    A = Matrix.from_csc(indptr, indices, values, nrows=d.size, ncols=d.size)
+    dv, r = Vector.from_dense(d), Vector.from_dense(r0)
+    w = Vector("FP32", d.size)
+    teleport = float(np.float32((1 - DAMPING) / d.size))
+    for _ in range(ITERS):
+        w << r.ewise_mult(dv, binary.truediv)
+        r[:] << teleport
+        r(binary.plus) << A.T.mxv(w, semiring.plus_times)
+    out, _ = r.to_dense(out=pinned)
+    h2d = indptr.nbytes + indices.nbytes + values.nbytes + d.nbytes + r0.nbytes
+    return out, h2d, out.nbytes
+
+
+def pinned_copy(arr):
+    """Copy a numpy array into page-locked host memory (kept alive by the returned torch tensor)."""
+    import torch
+
+    t = torch.empty(max(arr.nbytes, 1), dtype=torch.uint8, pin_memory=True)
+    out = t.numpy()[:arr.nbytes].view(arr.dtype).reshape(arr.shape)
+    out[...] = arr
+    return out, t
+
+
+def host_arrays(gb, job):
+    """CSC of A (= CSR of the pull matrix) + d exported from the device once, shared by the e2e and CPU legs."""
+    if getattr(job, "_host", None) is None:
+        ap, ai, ax = job.P.to_csc()
+        d, _ = job.d.to_dense()
+        job._host = (ap, ai, ax, d)
+    return job._host
+
+
+def measure_e2e(gb, job, args, r_dev):
+    import torch
+
+    ap, ai, ax, d = host_arrays(gb, job)
+    keep = []
+    host = []
+    for a in (ap, ai, ax, d, np.full(d.size, 1.0 / d.size, dtype=np.float32)):
+        h, t = pinned_copy(a)
+        host.append(h), keep.append(t)
+    out_pinned, t = pinned_copy(np.zeros(d.size, dtype=np.float32))
+    keep.append(t)
+    e2e_pagerank(gb, host, out_pinned)            # warm-up (allocator pools, lazy module load)
+    torch.cuda.synchronize()
+    steps = max(2, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out, h2d, d2h = e2e_pagerank(gb, host, out_pinned)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / steps
+    job._e2e_result = np.array(out)
+    return {"value": ITERS * ai.size / dt / 1e9, "unit": "GTEPS", "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": steps,
+            "path": "Matrix.from_csc(host uint64/f32) + Vector.from_dense x2 + 20 x [ewise_mult, assign, mxv] + to_dense"}
+
+
+def measure_cpu_baseline(gb, job, r_dev):
+    from oracle import oracle as O
+
+    O.build()
+    ap, ai, ax, d = host_arrays(gb, job)
+    n = d.size
+    P = O.Mat(ap.view(np.int64), ai.view(np.int64), ax, (n, n), "FP32")
+    iters = 3
+    r_cpu = cpu_pagerank(P, d, iters)                 # warm-up + the parity operand
+    done, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < 10.0:            # bounded sample: ~10 s of CPU work
+        cpu_pagerank(P, d, ITERS)
+        done += ITERS
+    dt = time.perf_counter() - t0
+    out = {"value": done * P.nnz / dt / 1e9, "unit": "GTEPS", "cores": O.num_threads(), "kind": "port",
+           "sample": f"{done} PageRank iterations ({done // ITERS} steps) on the same scale-{int(np.log2(n))} graph, {dt:.1f} s of CPU work"}
+    # parity of the bench workload itself: 3 iterations on the GPU vs the port, north_star tolerance 1e-5 relative
+    from graphblas_b200 import Vector, binary, semiring
+    r = Vector.from_dense(np.full(n, 1.0 / n, dtype=np.float32))
+    w = Vector("FP32", n)
+    for _ in range(iters):
+        w << r.ewise_mult(job.d, binary.truediv)
+        r[:] << job.teleport
+        r(binary.plus) << job.P.T.mxv(w, semiring.plus_times)
+    r_gpu, _ = r.to_dense()
+    out["parity_max_rel_err"] = float(np.max(np.abs(r_gpu.astype(np.float64) - r_cpu) / np.abs(r_cpu)))
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: libgrb_b200 has no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import graphblas_b200 as gb
+
+    gb.init("b200")
+    gb.use_torch_stream()
+    scale = args.scale + int(np.log2(world))
+    job = PageRankJob(gb, scale, rank, world)
+    nnz = job.nnz_total
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        job.reset()
+        job.step()
+    barrier()
+    # ---- timed region: K steps, device events, kernel timing on ----
+    gb.lib.GxB_b200_kernel_time_reset()
+    gb.set_option("timing", 1)
+    launches0 = gb.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        barrier()
+        ev0.record()
+        for _ in range(args.steps):
+            job.step()
+        ev1.record()
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    gb.set_option("timing", 0)
+    launches = gb.launch_count() - launches0
+    if args.breakdown and rank == 0:
+        gb.lib.GxB_b200_kernel_time_dump()
+    k_ms, k_cnt = kernel_time(gb, "spmv_pull")
+    f_ms, f_cnt = kernel_time(gb, "spmv_fixup")
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = ITERS * nnz / (ms_per_step * 1e-3) / 1e9
+    # ---- roofline of the dominant kernel (this rank's launches) ----
+    nb = job.hi - job.lo
+    alg_bytes = job.nnz_local * (4 + 4 + 4) + nb * (8 + 4 + 4)   # nnz*(I+V+X) + n*(P+Y) + accum read n*Y
+    peak, peak_src = measured_peaks()
+    achieved = alg_bytes / (k_ms / max(k_cnt, 1) * 1e-3) / 1e9 if k_cnt else None
+    line = {
+        "metric": METRIC, "value": value, "unit": "GTEPS", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(scale, nnz, world),
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "k_spmv_pull<plus_times,f32>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
+                     "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback 6650",
+                     "algorithmic_bytes_per_launch": int(alg_bytes), "avg_launch_ms": k_ms / max(k_cnt, 1),
+                     "launches_timed": k_cnt, "kernel_share_of_step": (k_ms / ms) if ms else None,
+                     "fixup_avg_launch_ms": f_ms / max(f_cnt, 1)},
+    }
+    traffic_file = os.path.join(ROOT, "profiles", "spmv_pull_traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            line["roofline"]["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    line["clocks"] = clk.summary()
+    if rank == 0 and world == 1:
+        r_dev, _ = job.r.to_dense()
+        if not args.no_e2e:
+            line["e2e"] = measure_e2e(gb, job, args, r_dev)
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = measure_cpu_baseline(gb, job, r_dev)
+    elif rank == 0:
+        line["e2e"] = None
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

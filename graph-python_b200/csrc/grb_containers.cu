@@ -9,15 +9,27 @@
 static inline int nblk(int64_t n, int b = 256) { return (int)cdiv(n > 0 ? n : 1, b); }
 
 // ---------------------------------------------------------------- object helpers
-GB_Object *obj_check(const void *h, const char *what) {
+GB_Object *obj_check_lazy(const void *h, const char *what) {
     if (!h) grb_throw(GrB_NULL_POINTER, std::string(what) + " is NULL");
     GB_Object *o = (GB_Object *)h;
     if (o->magic != GRB_MAGIC) grb_throw(o->magic == GRB_FREED ? GrB_UNINITIALIZED_OBJECT : GrB_INVALID_OBJECT,
                                          std::string(what) + " is not a valid object");
     return o;
 }
+GB_Object *obj_check(const void *h, const char *what) {
+    GB_Object *o = obj_check_lazy(h, what);
+    if (o->csr_stale) mat_ensure_csr(o);
+    return o;
+}
+void mat_ensure_csr(GB_Object *o) {
+    if (!o->csr_stale) return;
+    csr_free(o->csr);
+    csr_transpose(o->csc, o->csr, o->type->size);
+    o->csr_stale = false;
+}
 
 void obj_invalidate_caches(GB_Object *o) {
+    o->csr_stale = false;
     if (o->csc_valid) { csr_free(o->csc); o->csc_valid = false; }
     dfree(o->csr.tile_row); o->csr.tile_row = nullptr; o->csr.ntiles = 0;
 }
@@ -169,13 +181,14 @@ GrB_Info GrB_Matrix_ncols(GrB_Index *ncols, const GrB_Matrix A) {
 GrB_Info GrB_Matrix_nvals(GrB_Index *nvals, const GrB_Matrix A) {
     if (!nvals) return GrB_NULL_POINTER;
     API_BEGIN
-    *nvals = (GrB_Index)obj_nvals(obj_check(A, "A"));
+    GB_Object *o = obj_check_lazy(A, "A");
+    *nvals = (GrB_Index)(o->csr_stale ? o->csc.nnz : obj_nvals(o));
     API_END(A)
 }
 GrB_Info GrB_Matrix_wait(GrB_Matrix A, GrB_WaitMode mode) {
     (void)mode;
     API_BEGIN
-    obj_check(A, "A");
+    obj_check_lazy(A, "A");
     stream_sync();
     API_END(A)
 }
@@ -542,10 +555,8 @@ static GrB_Info matrix_import(GrB_Matrix *A_, GrB_Type type, GrB_Index nrows, Gr
         } else if (format == GrB_CSC_FORMAT) {
             Csr t = csr_from_host(A->ncols, A->nrows, Ap, Ai, Ax, (int64_t)Ap_len, (int64_t)Ai_len, (int64_t)Ax_len,
                                   xcode, code, false, true);
-            Csr c;
-            csr_transpose(t, c, type->size);
-            mat_set_csr(A, c);
-            A->csc = t; A->csc_valid = true;
+            // keep the columns only; rows are built on first use (A.T.mxv / u.vxm(A) never need them)
+            A->csc = t; A->csc_valid = true; A->csr_stale = true;
         } else if (format == GrB_COO_FORMAT) {
             // C API 2.0 COO import: Ap = row indices, Ai = column indices
             coo_from_host_into(A, Ap, Ai, Ax, (int64_t)Ax_len, xcode);

@@ -53,6 +53,42 @@ static GB_Type_opaque type_tab[TC_COUNT] = {
 #define TCODE_FP32 TC_FP32
 #define TCODE_FP64 TC_FP64
 
+// ---------------------------------------------------------------- per-kernel device timing
+// A ring of CUDA event pairs recorded on g.stream around each launch while g.timing != 0; folded into
+// per-name totals when the ring fills or when a total is read.  bench.py uses it for roofline.achieved.
+struct KtName { const char *name; double ms; uint64_t count; };
+struct KtPending { cudaEvent_t a, b; int name_idx; };
+static std::vector<KtName> kt_names;
+static std::vector<KtPending> kt_ring;
+static int kt_used = 0;
+static const int KT_RING = 2048;
+static void ktime_fold() {
+    if (kt_used == 0) return;
+    cudaEventSynchronize(kt_ring[kt_used - 1].b);
+    for (int i = 0; i < kt_used; i++) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, kt_ring[i].a, kt_ring[i].b) == cudaSuccess) {
+            kt_names[kt_ring[i].name_idx].ms += ms;
+            kt_names[kt_ring[i].name_idx].count++;
+        }
+    }
+    kt_used = 0;
+}
+int ktime_begin(const char *name) {
+    if ((int)kt_ring.size() < KT_RING) {
+        kt_ring.resize(KT_RING);
+        for (auto &p : kt_ring) { cudaEventCreate(&p.a); cudaEventCreate(&p.b); }
+    }
+    if (kt_used == KT_RING) ktime_fold();
+    int idx = -1;
+    for (size_t i = 0; i < kt_names.size(); i++) if (kt_names[i].name == name || !strcmp(kt_names[i].name, name)) { idx = (int)i; break; }
+    if (idx < 0) { kt_names.push_back({name, 0.0, 0}); idx = (int)kt_names.size() - 1; }
+    kt_ring[kt_used].name_idx = idx;
+    cudaEventRecord(kt_ring[kt_used].a, g.stream);
+    return kt_used++;
+}
+void ktime_end(int slot) { cudaEventRecord(kt_ring[slot].b, g.stream); }
+
 extern "C" {
 #define X(NAME, CT, CODE) GrB_Type GrB_##NAME = &type_tab[CODE];
 GRB_TYPE_LIST(X)
@@ -238,11 +274,32 @@ GrB_Info GxB_b200_device_info(int *device, int *sm_count, size_t *free_bytes, si
 }
 uint64_t GxB_b200_launch_count(void) { return g.launches; }
 const char *GxB_b200_last_kernel(void) { return g.last_kernel; }
+GrB_Info GxB_b200_kernel_time(const char *name, double *total_ms, uint64_t *launches) {
+    if (!name || !total_ms || !launches) return GrB_NULL_POINTER;
+    ktime_fold();
+    *total_ms = 0; *launches = 0;
+    for (auto &k : kt_names)
+        if (!strcmp(k.name, name)) { *total_ms += k.ms; *launches += k.count; }
+    return GrB_SUCCESS;
+}
+GrB_Info GxB_b200_kernel_time_dump(void) {
+    ktime_fold();
+    for (auto &k : kt_names)
+        fprintf(stderr, "[grb_b200 timing] %-28s launches=%8llu total_ms=%10.3f avg_us=%9.2f\n", k.name,
+                (unsigned long long)k.count, k.ms, k.count ? 1e3 * k.ms / k.count : 0.0);
+    return GrB_SUCCESS;
+}
+GrB_Info GxB_b200_kernel_time_reset(void) {
+    ktime_fold();
+    kt_names.clear();
+    return GrB_SUCCESS;
+}
 GrB_Info GxB_b200_set_option(const char *name, int64_t value) {
     if (!name) return GrB_NULL_POINTER;
     if (!strcmp(name, "push_ratio")) g.push_ratio = value;
     else if (!strcmp(name, "force_direction")) g.force_direction = value;
     else if (!strcmp(name, "burble")) g.burble = value;
+    else if (!strcmp(name, "timing")) { if (!value) ktime_fold(); g.timing = value; }
     else return GrB_INVALID_VALUE;
     return GrB_SUCCESS;
 }

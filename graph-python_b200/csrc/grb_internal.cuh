@@ -74,6 +74,7 @@ struct GB_Object {
     Csr csr;             // A by rows
     Csr csc;             // A' by rows (== A by columns), valid iff csc_valid
     bool csc_valid = false;
+    bool csr_stale = false;   // imported by columns: only csc is populated until somebody needs rows (mat_ensure_csr)
     // ---- dense vector / scalar storage (n = nrows) ----
     void *vals = nullptr;
     uint8_t *present = nullptr;
@@ -124,16 +125,22 @@ struct GrbGlobal {
     int64_t push_ratio = 24;       // push when nvals(u) * push_ratio < n
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
     int64_t burble = 0;
+    int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
     // scratch
     int64_t *d_scratch = nullptr;  // 64 int64 of device scratch (counters)
     int64_t *h_pinned = nullptr;   // 64 int64 of pinned host memory for small read-backs
 };
 extern GrbGlobal g;
+// per-kernel-name device timing (grb_context.cu): events on g.stream around each launch while g.timing is set
+int ktime_begin(const char *name);
+void ktime_end(int slot);
 
 // every kernel launch goes through this macro: counts launches (bench.py's gpu_launches) and names the path
 #define GRB_LAUNCH(name, kernel, grid, block, smem, ...)                             \
     do {                                                                             \
+        const int _slot = g.timing ? ktime_begin(name) : -1;                         \
         kernel<<<(grid), (block), (smem), g.stream>>>(__VA_ARGS__);                  \
+        if (_slot >= 0) ktime_end(_slot);                                            \
         g.launches++;                                                                \
         g.last_kernel = name;                                                        \
         if (g.burble) fprintf(stderr, "[grb_b200] %s grid=%lld block=%d\n", name, (long long)(grid), (int)(block)); \
@@ -152,7 +159,9 @@ void stream_sync();
 int64_t read_i64(const int64_t *dptr);   // synchronising read-back of one device int64
 
 // ---- object helpers (grb_containers.cu) ----
-GB_Object *obj_check(const void *h, const char *what);   // NULL -> GrB_NULL_POINTER, bad magic -> INVALID_OBJECT
+GB_Object *obj_check(const void *h, const char *what);   // NULL -> GrB_NULL_POINTER, bad magic -> INVALID_OBJECT; materialises a stale CSR
+GB_Object *obj_check_lazy(const void *h, const char *what);   // same, but leaves a column-imported matrix as it is (hot paths pick a side)
+void mat_ensure_csr(GB_Object *o);                        // rows of A from the cached columns, if A was imported by columns
 void csr_free(Csr &c);
 void obj_release_storage(GB_Object *o);
 void obj_invalidate_caches(GB_Object *o);                 // after the CSR changed: drop csc + tiles

@@ -45,7 +45,7 @@ struct View {
 static void view_of(View &v, GB_Object *A, bool transpose) {
     if (A->kind != K_MATRIX) { Csr c = transpose ? vec_as_csr_row(A) : vec_as_csr_column(A); v.adopt(c); }
     else if (transpose) { mat_ensure_csc(A); v.csr = &A->csc; }
-    else v.csr = &A->csr;
+    else { mat_ensure_csr(A); v.csr = &A->csr; }
 }
 static void view_cast(View &v, int from_code, int to_code, size_t from_size) {
     if (from_code == to_code) return;
@@ -325,7 +325,7 @@ extern "C" {
 GrB_Info GrB_mxm(GrB_Matrix C, const GrB_Matrix Mask, const GrB_BinaryOp accum, const GrB_Semiring op, const GrB_Matrix A,
                  const GrB_Matrix B, const GrB_Descriptor desc) {
     API_BEGIN
-    GB_Object *Cobj = obj_check(C, "C"), *Aobj = obj_check(A, "A"), *Bobj = obj_check(B, "B");
+    GB_Object *Cobj = obj_check(C, "C"), *Aobj = obj_check_lazy(A, "A"), *Bobj = obj_check_lazy(B, "B");
     GB_Object *M = Mask ? obj_check(Mask, "Mask") : nullptr;
     matrix_product(Cobj, M, accum, op, Aobj, Bobj, desc_flags(desc));
     API_END(C)

@@ -98,6 +98,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     auto get_csr = [&](bool want_transpose) -> Csr * {
         if (Aoverride) return nullptr;
         if (want_transpose) { mat_ensure_csc(Aobj); return &Aobj->csc; }
+        mat_ensure_csr(Aobj);
         return &Aobj->csr;
     };
 
@@ -242,6 +243,7 @@ static void vector_product(GB_Object *w, GB_Object *mask, const GrB_BinaryOp acc
     GB_Object castA;
     bool castA_on = false;
     if (A->type->code != tcode) {
+        mat_ensure_csr(A);
         castA.kind = K_MATRIX; castA.nrows = A->nrows; castA.ncols = A->ncols;
         static GB_Type_opaque cast_types[TC_COUNT];
         cast_types[tcode] = {tcode, kTypeSize[tcode], "cast"};
@@ -263,7 +265,7 @@ extern "C" {
 GrB_Info GrB_mxv(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Semiring op,
                  const GrB_Matrix A, const GrB_Vector u, const GrB_Descriptor desc) {
     API_BEGIN
-    GB_Object *W = obj_check(w, "w"), *Aobj = obj_check(A, "A"), *U = obj_check(u, "u");
+    GB_Object *W = obj_check(w, "w"), *Aobj = obj_check_lazy(A, "A"), *U = obj_check(u, "u");
     GB_Object *M = mask ? obj_check(mask, "mask") : nullptr;
     vector_product(W, M, accum, op, Aobj, U, desc_flags(desc), false);
     API_END(w)
@@ -272,7 +274,7 @@ GrB_Info GrB_mxv(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, 
 GrB_Info GrB_vxm(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Semiring op,
                  const GrB_Vector u, const GrB_Matrix A, const GrB_Descriptor desc) {
     API_BEGIN
-    GB_Object *W = obj_check(w, "w"), *Aobj = obj_check(A, "A"), *U = obj_check(u, "u");
+    GB_Object *W = obj_check(w, "w"), *Aobj = obj_check_lazy(A, "A"), *U = obj_check(u, "u");
     GB_Object *M = mask ? obj_check(mask, "mask") : nullptr;
     vector_product(W, M, accum, op, Aobj, U, desc_flags(desc), true);
     API_END(w)

@@ -172,6 +172,14 @@ def _initialize():
                 op = _get(ns, cls, a)
                 if "BOOL" not in op._typed:
                     op._typed["BOOL"] = base._typed["BOOL"]
+    # binary.truediv: true division, defined on the floating-point types where it equals GrB_DIV (the reference
+    # builds it for integers too by casting to FP64, graphblas/core/operator/binary.py; not needed on this path)
+    div = getattr(binary, "div", None)
+    if div is not None:
+        td = _get(binary, BinaryOp, "truediv")
+        for t in ("FP32", "FP64"):
+            if t in div._typed:
+                td._typed[t] = div._typed[t]
 
 
 _initialize()

@@ -88,7 +88,7 @@ def test_writeback_semantics_vs_oracle(gb, direction, accum, replace, comp, stru
     from graphblas_b200 import binary, semiring
 
     rng = np.random.default_rng(7)
-    n = 3000
+    n = 1500
     dt = "INT64"
     A = O.rmat_matrix(11, dt, value_mode=1)
     A = O.Mat(A.indptr[: n + 1], A.indices[: A.indptr[n]] % n, A.values[: A.indptr[n]], (n, n), dt)
