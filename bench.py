@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel device times of the timed region to stderr")
+    ap.add_argument("--hub-mode", type=int, default=None, help="libgrb_b200 option hub_mode (0 off, 1 auto, 2 always)")
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
     return ap.parse_args()
 
@@ -382,6 +383,8 @@ def run_b200(args):
 
     gb.init("b200")
     gb.use_torch_stream()
+    if args.hub_mode is not None:
+        gb.set_option("hub_mode", args.hub_mode)
     scale = args.scale + int(np.log2(world))
     job = PageRankJob(gb, scale, rank, world)
     nnz = job.nnz_total

@@ -31,7 +31,7 @@ void mat_ensure_csr(GB_Object *o) {
 void obj_invalidate_caches(GB_Object *o) {
     o->csr_stale = false;
     if (o->csc_valid) { csr_free(o->csc); o->csc_valid = false; }
-    dfree(o->csr.tile_row); o->csr.tile_row = nullptr; o->csr.ntiles = 0;
+    csr_drop_caches(o->csr);
 }
 
 void obj_release_storage(GB_Object *o) {

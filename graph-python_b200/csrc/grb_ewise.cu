@@ -49,18 +49,48 @@ static void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f,
     dzero(w->d_nvals, sizeof(int64_t));
     GRB_TYPE_SWITCH(wcode, W, {
         EpiArgs<W> e = epi_for<W>(w, mask, f, accum);
-        GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, nblk(n), 256, 0, e, (const W *)t, tp, n);
+        GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, ew_grid4(n), 256, 0, e, (const W *)t, tp, n);
     });
     dfree(tc);
     vec_set_unknown_nvals(w);
 }
 
+// C typecast of one scalar on the host, matching cast_array's device rules (float -> integer saturates, NaN -> 0,
+// anything -> bool is "!= 0")
+template <class W, class T> static inline W host_cast(T x) {
+    if constexpr (std::is_same<W, bool>::value) return x != (T)0;
+    else if constexpr (std::is_floating_point<T>::value && std::is_integral<W>::value) {
+        if (x != x) return (W)0;
+        const double lo = (double)std::numeric_limits<W>::lowest(), hi = (double)std::numeric_limits<W>::max();
+        const double v = (double)x;
+        if (v <= lo) return std::numeric_limits<W>::lowest();
+        if (v >= hi) return std::numeric_limits<W>::max();
+        return (W)v;
+    } else return (W)x;
+}
+
 // ---------------------------------------------------------------- assign
 template <class T>
 __global__ void __launch_bounds__(256) k_assign_scalar(EpiArgs<T> e, T x, int64_t n) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int c = 0;
-    if (i < n) c = epi_store(e, i, epi_allowed(e, i), true, x);
+    const bool need_old = epi_needs_old(e);
+    const int64_t base = blockIdx.x * (int64_t)(256 * EW_VEC) + threadIdx.x;
+    // plain fill (no mask, no accumulator): nothing to read at all
+    if (!e.mask_p && !e.comp && e.accum < 0) {
+#pragma unroll
+        for (int k = 0; k < EW_VEC; k++) { const int64_t i = base + k * 256; if (i < n) { e.w_out[i] = x; e.wp_out[i] = 1; c++; } }
+        block_count_add(e.count, c);
+        return;
+    }
+    bool al[EW_VEC], wh[EW_VEC]; T wo[EW_VEC];
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) {
+        const int64_t i = base + k * 256;
+        al[k] = wh[k] = false; wo[k] = (T)0;
+        if (i < n) { al[k] = epi_allowed(e, i); wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+    }
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) { const int64_t i = base + k * 256; if (i < n) c += epi_apply(e, i, al[k], true, x, wh[k], wo[k]); }
     block_count_add(e.count, c);
 }
 // w(I)<m> = accum(w(I), x) for an explicit index list: positions outside I are left alone
@@ -85,22 +115,22 @@ static GrB_Info vector_assign_scalar(GrB_Vector w_, const GrB_Vector mask_, cons
     DescFlags f = desc_flags(desc);
     int acc = accum_code(accum);
     int64_t n = w->nrows;
-    // value in w's type
-    void *dx = dmalloc(16);
-    h2d(dx, &x, sizeof(T));
-    void *dxc = dmalloc(16);
-    cast_array(dx, xcode, dxc, w->type->code, 1);
+    // value in w's type (C typecast rules, on the host: no device round trip, no synchronisation)
     char hx[8];
-    d2h(hx, dxc, w->type->size);
-    stream_sync();
-    dfree(dx); dfree(dxc);
+    (void)xcode;
+    GRB_TYPE_SWITCH(w->type->code, W, { W xv = host_cast<W, T>(x); memcpy(hx, &xv, sizeof(W)); });
     const bool all = (I == GrB_ALL);
     GRB_TYPE_SWITCH(w->type->code, W, {
         W xv; memcpy(&xv, hx, sizeof(W));
         EpiArgs<W> e = epi_for<W>(w, mask, f, acc);
-        if (all) {
+        if (all && !mask && !f.comp) {
+            // every position receives an entry: nvals is known without counting (and without a later read-back)
+            e.count = nullptr;
+            GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, ew_grid4(n), 256, 0, e, xv, n);
+            w->nvals = n; w->nvals_known = true; w->list_valid = false;
+        } else if (all) {
             dzero(w->d_nvals, sizeof(int64_t));
-            GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, nblk(n), 256, 0, e, xv, n);
+            GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, ew_grid4(n), 256, 0, e, xv, n);
             vec_set_unknown_nvals(w);
         } else {
             if (f.replace) grb_throw(GrB_NOT_IMPLEMENTED, "assign with an index list and replace");
@@ -141,6 +171,40 @@ __global__ void __launch_bounds__(256) k_ewise(const T *u, const uint8_t *up, co
     }
 }
 
+// fused form: t = u op v computed per element and handed straight to the write-back (w's type == the op's z type)
+template <class X, class Z, bool UNION, bool CMP>
+__global__ void __launch_bounds__(256) k_ewise_fused(const X *u, const uint8_t *up, const X *v, const uint8_t *vp, int op,
+                                                     EpiArgs<Z> e, int64_t n) {
+    int c = 0;
+    const bool need_old = epi_needs_old(e);
+    const int64_t base = blockIdx.x * (int64_t)(256 * EW_VEC) + threadIdx.x;
+    bool pa[EW_VEC], pb[EW_VEC], al[EW_VEC], wh[EW_VEC]; X xv[EW_VEC], yv[EW_VEC]; Z wo[EW_VEC];
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) {      // all loads of the batch first: 4 x the memory-level parallelism
+        const int64_t i = base + k * 256;
+        pa[k] = pb[k] = al[k] = wh[k] = false; xv[k] = yv[k] = (X)0; wo[k] = (Z)0;
+        if (i < n) {
+            pa[k] = up[i] != 0; pb[k] = vp[i] != 0; xv[k] = u[i]; yv[k] = v[i];
+            al[k] = epi_allowed(e, i); wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) {
+        const int64_t i = base + k * 256;
+        if (i >= n) continue;
+        const bool a = pa[k], b = pb[k];
+        const bool has = UNION ? (a || b) : (a && b);
+        Z t = (Z)0;
+        if (has) {
+            const X x = xv[k], y = yv[k];
+            if constexpr (CMP) t = (Z)((a && b) ? cmp_rt<X>(op, x, y) : (a ? (x != (X)0) : (y != (X)0)));
+            else t = (Z)((a && b) ? binop_rt<X>(op, x, y) : (a ? x : y));
+        }
+        c += epi_apply(e, i, al[k], has, t, wh[k], wo[k]);
+    }
+    block_count_add(e.count, c);
+}
+
 static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_BinaryOp op,
                          const GrB_Vector u_, const GrB_Vector v_, const GrB_Descriptor desc, bool is_union) {
     require_init();
@@ -158,6 +222,30 @@ static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_Binary
     const void *uv = u->vals, *vv = v->vals;
     if (u->type->code != xcode) { uc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(u->vals, u->type->code, uc, xcode, n); uv = uc; }
     if (v->type->code != xcode) { vc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(v->vals, v->type->code, vc, xcode, n); vv = vc; }
+    if (w->type->code == zcode) {
+        // both operands full and no mask: the result is full, nvals needs no counting
+        const bool known_full = !mask && !f.comp && u->nvals_known && v->nvals_known && u->nvals == n && v->nvals == n;
+        if (!known_full) dzero(w->d_nvals, sizeof(int64_t));
+        GRB_TYPE_SWITCH(xcode, X, {
+            if (cmp) {
+                EpiArgs<bool> e = epi_for<bool>(w, mask, f, acc);
+                if (known_full) e.count = nullptr;
+                auto kern = is_union ? k_ewise_fused<X, bool, true, true> : k_ewise_fused<X, bool, false, true>;
+                GRB_LAUNCH(is_union ? "ewise_add" : "ewise_mult", kern, ew_grid4(n), 256, 0, (const X *)uv, u->present,
+                           (const X *)vv, v->present, op->op, e, n);
+            } else {
+                EpiArgs<X> e = epi_for<X>(w, mask, f, acc);
+                if (known_full) e.count = nullptr;
+                auto kern = is_union ? k_ewise_fused<X, X, true, false> : k_ewise_fused<X, X, false, false>;
+                GRB_LAUNCH(is_union ? "ewise_add" : "ewise_mult", kern, ew_grid4(n), 256, 0, (const X *)uv, u->present,
+                           (const X *)vv, v->present, op->op, e, n);
+            }
+        });
+        if (known_full) { w->nvals = n; w->nvals_known = true; w->list_valid = false; }
+        else vec_set_unknown_nvals(w);
+        dfree(uc); dfree(vc);
+        return;
+    }
     void *t = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[zcode]);
     uint8_t *tp = dalloc<uint8_t>(n);
     GRB_TYPE_SWITCH(xcode, X, {

@@ -63,6 +63,17 @@ struct Csr {
     int32_t *tile_row = nullptr;
     int64_t ntiles = 0;
     int tile_nnz = 0;
+    // hub cache for the pull kernel (csr_ensure_hubs): the hub_n most referenced columns, and a copy of colidx in
+    // which those columns are replaced by 0x80000000 | rank.  Built after the matrix has been pulled from twice.
+    uint32_t *hub_ids = nullptr;
+    uint32_t *hub_col = nullptr;   // bit 31: hub (low bits = rank); bit 30: first entry of its row; else the column
+    int hub_n = 0;
+    int pull_uses = 0;
+    uint32_t *nzrow = nullptr;     // ids of the rows that have entries, ascending
+    int64_t n_nzrow = 0;
+    int64_t *tile_first = nullptr; // [stream tiles + 1] rows of nzrow that start before the tile
+    uint32_t *chunk_first = nullptr;   // [ceil(nnz / 8)] index in nzrow of the row that owns entry 8 * i
+    int64_t n_stiles = 0;
 };
 
 struct GB_Object {
@@ -124,6 +135,7 @@ struct GrbGlobal {
     // tunables (GxB_b200_set_option)
     int64_t push_ratio = 24;       // push when nvals(u) * push_ratio < n
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
+    int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
     int64_t burble = 0;
     int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
     // scratch
@@ -173,6 +185,8 @@ void vec_build_list(GB_Object *o);                        // dense -> sorted ind
 void mat_ensure_csc(GB_Object *o);                        // build + cache the transpose on the device
 void csr_transpose(const Csr &a, Csr &t, size_t tsize);
 void csr_ensure_tiles(Csr &c, int tile_nnz);
+void csr_ensure_hubs(Csr &c, int capacity);               // build / rebuild the hub cache for at most `capacity` hubs
+void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)
 void mat_set_csr(GB_Object *o, Csr &c);                   // take ownership of c as o's CSR
 Csr csr_dup(const Csr &a, size_t tsize);
 Csr vec_as_csr_column(GB_Object *v);                      // n x 1 matrix view of a vector (copy)

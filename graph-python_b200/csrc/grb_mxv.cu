@@ -22,6 +22,26 @@ bool spmv_launch_pull(int mon, int mul, int tcode, const void *pa, int mode) {
     }
     return false;
 }
+bool spmv_launch_stream(int mon, int mul, int tcode, const void *sa) {
+    switch (mon) {
+    case OP_PLUS: return spmv_stream_PLUS(mul, tcode, sa);
+    case OP_MIN: return spmv_stream_MIN(mul, tcode, sa);
+    case OP_MAX: return spmv_stream_MAX(mul, tcode, sa);
+    case OP_ANY: return spmv_stream_ANY(mul, tcode, sa);
+    case OP_LOR: case OP_LAND: case OP_LXOR: case OP_LXNOR: return spmv_stream_BOOLMON(mul | (mon << 8), tcode, sa);
+    }
+    return false;
+}
+bool spmv_launch_red(int mon, int mul, int tcode, const void *ra) {
+    switch (mon) {
+    case OP_PLUS: return spmv_red_PLUS(mul, tcode, ra);
+    case OP_MIN: return spmv_red_MIN(mul, tcode, ra);
+    case OP_MAX: return spmv_red_MAX(mul, tcode, ra);
+    case OP_ANY: return spmv_red_ANY(mul, tcode, ra);
+    case OP_LOR: case OP_LAND: case OP_LXOR: case OP_LXNOR: return spmv_red_BOOLMON(mul | (mon << 8), tcode, ra);
+    }
+    return false;
+}
 bool spmv_launch_push(int mon, int mul, int tcode, const void *pa) {
     switch (mon) {
     case OP_PLUS: return spmv_push_PLUS(mul, tcode, pa);
@@ -109,14 +129,14 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         dzero(w->d_nvals, sizeof(int64_t));
         if (fused) {
             EpiArgs<T> e = make_epi<T>(w, false, mask, f, accum);
-            GRB_LAUNCH("vec_writeback", k_vec_writeback<T>, nblk(n_out), 256, 0, e, tv, tpres, n_out);
+            GRB_LAUNCH("vec_writeback", k_vec_writeback<T>, ew_grid4(n_out), 256, 0, e, tv, tpres, n_out);
         } else {
             int wcode = w->type->code;
             void *tc = dmalloc((size_t)(n_out > 0 ? n_out : 1) * w->type->size);
             cast_array(tv, tcode, tc, wcode, n_out);
             GRB_TYPE_SWITCH(wcode, W, {
                 EpiArgs<W> e = make_epi<W>(w, false, mask, f, accum);
-                GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, nblk(n_out), 256, 0, e, (const W *)tc, tpres, n_out);
+                GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, ew_grid4(n_out), 256, 0, e, (const W *)tc, tpres, n_out);
             });
             dfree(tc);
         }
@@ -126,7 +146,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     if (push) {
         t = dalloc<T>(n_out); tp = dalloc<uint8_t>(n_out);
         T ident = monoid_identity<T>(mon);
-        GRB_LAUNCH("fill_identity", k_fill_identity<T>, nblk(n_out), 256, 0, t, tp, n_out, ident);
+        GRB_LAUNCH("fill_identity", k_fill_identity<T>, ew_grid(n_out), 256, 0, t, tp, n_out, ident);
         if (nu > 0) {
             vec_build_list(u);
             const Csr *M = Aoverride ? Aoverride : get_csr(!use_transpose);
@@ -162,19 +182,91 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     a.nrows = M->nrows; a.nnz = M->nnz;
     a.carry_head = a.carry_own = nullptr; a.carry_head_has = a.carry_own_has = nullptr;
     a.tile_row = nullptr; a.ntiles = 0;
-    if (!pull_any) {
+    a.hub_v = nullptr; a.hub_p = nullptr; a.hub_n = 0;
+    // flagged-stream fast path: u full, and the matrix is pulled from repeatedly (iterative algorithms) so that
+    // building its stream form (hub ranks, row-start flags) pays off
+    bool use_stream = !pull_any && a.up == nullptr && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
+    if (use_stream) {
+        M->pull_uses++;
+        if (g.hub_mode == 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20))) csr_ensure_hubs(*M, hub_capacity<T>());
+        use_stream = M->hub_col != nullptr && M->hub_n <= hub_capacity<T>();
+    }
+    // ---- atomic-segment pull: no mask, and the write-back is the monoid itself (or a plain overwrite) ----
+    if (use_stream && !have_mask && !f.comp && (accum < 0 || accum == mon)) {
+        const bool pingpong = fused && ((w == u) || (u_vals == w->vals));
+        RedArgs<T> ra;
+        ra.pcol = M->hub_col; ra.av = (const T *)M->vals; ra.a_iso = M->iso; ra.u = (const T *)u_vals;
+        ra.hub_n = M->hub_n; ra.nzrow = M->nzrow; ra.chunk_first = M->chunk_first; ra.nnz = M->nnz; ra.ntiles = M->n_stiles;
+        T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
+        GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, (const uint8_t *)nullptr, M->hub_ids, ra.hub_n, hv, hp);
+        ra.hub_v = hv;
+        const T ident = monoid_identity<T>(mon);
+        const bool overwrite = !fused || accum < 0;
+        const bool w_full = fused && w->nvals_known && w->nvals == n_out;
+        if (fused) {
+            if (pingpong) {
+                vec_ensure_alt(w);
+                if (!overwrite) { d2d(w->vals_alt, w->vals, (size_t)n_out * sizeof(T)); d2d(w->present_alt, w->present, (size_t)n_out); }
+                ra.w = (T *)w->vals_alt; ra.wp = w->present_alt;
+            } else { ra.w = (T *)w->vals; ra.wp = w->present; }
+        } else {
+            t = dalloc<T>(n_out); tp = dalloc<uint8_t>(n_out);
+            ra.w = t; ra.wp = tp;
+        }
+        if (overwrite || !w_full)
+            GRB_LAUNCH("red_prefill", k_red_prefill<T>, ew_grid(n_out), 256, 0, ra.w, ra.wp, n_out, ident, (int)overwrite);
+        if (!overwrite && w_full) ra.wp = nullptr;     // stays full: no presence traffic at all
+        const bool ok = spmv_launch_red(mon, mul, tcode, &ra);
+        dfree(hv); dfree(hp);
+        if (!ok) { dfree(t); dfree(tp); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
+        if (fused) {
+            if (pingpong) swap_pingpong(w);
+            if (overwrite) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
+            else if (w_full) { w->list_valid = false; }
+            else { count_present(w->present, n_out, w->d_nvals); vec_set_unknown_nvals(w); }
+        } else {
+            writeback(t, tp);
+            dfree(t); dfree(tp);
+        }
+        return;
+    }
+    StreamArgs<T> sa;
+    if (use_stream) {
+        sa.rowptr = M->rowptr; sa.pcol = M->hub_col; sa.av = (const T *)M->vals; sa.a_iso = M->iso;
+        sa.u = (const T *)u_vals; sa.hub_n = M->hub_n;
+        sa.nzrow = M->nzrow; sa.tile_first = M->tile_first; sa.nrows = M->nrows; sa.nnz = M->nnz; sa.ntiles = M->n_stiles;
+        T *hv = dalloc<T>(sa.hub_n); uint8_t *hp = dalloc<uint8_t>(sa.hub_n);
+        GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(sa.hub_n), 256, 0, sa.u, (const uint8_t *)nullptr, M->hub_ids, sa.hub_n, hv, hp);
+        sa.hub_v = hv; a.hub_v = hv; a.hub_p = hp;
+        sa.carry_head = dalloc<T>(2 * sa.ntiles); sa.carry_own = sa.carry_head + sa.ntiles;
+        a.carry_head = sa.carry_head;
+        sa.open_list = dalloc<int32_t>(sa.ntiles + 1); sa.open_count = (int *)(sa.open_list + sa.ntiles);
+        dzero(sa.open_count, sizeof(int));
+    }
+    if (!pull_any && !use_stream) {
         csr_ensure_tiles(*M, SPMV_TILE);
         a.tile_row = M->tile_row; a.ntiles = M->ntiles;
         a.carry_head = dalloc<T>(2 * M->ntiles); a.carry_own = a.carry_head + M->ntiles;
         a.carry_head_has = dalloc<uint8_t>(2 * M->ntiles); a.carry_own_has = a.carry_head_has + M->ntiles;
     }
+    auto launch = [&](const EpiArgs<T> &e) {
+        bool ok;
+        if (use_stream) {
+            sa.epi = e;
+            ok = spmv_launch_stream(mon, mul, tcode, &sa);
+            if (ok && M->n_nzrow < M->nrows)
+                GRB_LAUNCH("stream_empty_rows", k_stream_empty_rows<T>, ew_grid(M->nrows), 256, 0, M->rowptr, M->nrows, e);
+        } else {
+            a.epi = e;
+            ok = spmv_launch_pull(mon, mul, tcode, &a, pull_any ? PULL_ANY : PULL_STREAM);
+        }
+        if (!ok) grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel");
+    };
     if (fused) {
         // w aliasing u (e.g. w(min) << w.vxm(A)): write to the ping-pong spare, then swap
         const bool pingpong = (w == u) || (u_vals == w->vals);
-        a.epi = make_epi<T>(w, pingpong, mask, f, accum);
         dzero(w->d_nvals, sizeof(int64_t));
-        if (!spmv_launch_pull(mon, mul, tcode, &a, pull_any ? PULL_ANY : PULL_STREAM))
-            grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel");
+        launch(make_epi<T>(w, pingpong, mask, f, accum));
         if (pingpong) swap_pingpong(w);
         vec_set_unknown_nvals(w);
     } else {
@@ -187,13 +279,12 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         e.count = (unsigned long long *)(g.d_scratch + 16);
         if (pull_any) { e.mask_p = mask->present; e.mask_v = mask->vals; e.mask_vsize = f.structure ? 0 : (int)mask->type->size;
                         e.mask_fp = (mask->type->code == TC_FP32 || mask->type->code == TC_FP64); e.comp = f.comp; }
-        a.epi = e;
-        if (!spmv_launch_pull(mon, mul, tcode, &a, pull_any ? PULL_ANY : PULL_STREAM))
-            grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel");
+        launch(e);
         writeback(t, tp);
         dfree(t); dfree(tp);
     }
-    if (!pull_any) { dfree(a.carry_head); dfree(a.carry_head_has); }
+    if (use_stream) dfree(sa.open_list);
+    if (!pull_any) { dfree(a.carry_head); dfree(a.carry_head_has); dfree((void *)a.hub_v); dfree((void *)a.hub_p); }
 }
 
 // shared body of GrB_mxv / GrB_vxm

@@ -1,11 +1,12 @@
 // grb_spmv.cuh — the vector-product kernels behind GrB_mxv / GrB_vxm.
 //
-//   k_spmv_pull      streaming pull: every CTA owns one contiguous tile of TILE_NNZ matrix entries, reads
-//                    indices/values fully coalesced exactly once, gathers u (L2-resident), stages the
-//                    products in shared memory, reduces the rows that start in the tile and runs the fused
-//                    write-back w<m,replace> = accum(w, t) for them.  Rows that cross tile borders leave a
-//                    partial in carry[]; k_spmv_fixup (one warp per tile) finishes those rows.
-//                    HBM-bound: algorithmic bytes = nnz*(4 + V + X) + n*(8 + Y) (+ mask / accum reads).
+//   k_spmv_pull      persistent streaming pull: one CTA per SM, every warp walks tiles of 256 consecutive matrix
+//                    entries, reads indices/values coalesced exactly once, gathers u (the most referenced "hub"
+//                    entries from a shared-memory table, the rest from L2), stages the products in its private
+//                    shared-memory strip, reduces the rows that start in the tile and runs the fused write-back
+//                    w<m,replace> = accum(w, t) for them.  Rows that cross tile borders leave a partial in
+//                    carry[]; k_spmv_fixup (one warp per tile) finishes those rows.
+//                    Algorithmic bytes = nnz*(4 + V + X) + n*(8 + Y) (+ mask / accum reads).
 //   k_pull_any       masked pull with early exit for the ANY monoid (BFS bottom-up): one thread per
 //                    allowed row stops at its first parent; bytes = edges actually scanned.
 //   k_push_scatter   sparse-frontier push: edge-balanced (load-balanced search over the frontier's degree
@@ -18,9 +19,6 @@
 #include "grb_internal.cuh"
 #include "grb_ops.cuh"
 
-constexpr int SPMV_THREADS = 256;
-constexpr int SPMV_PER_THREAD = 8;
-constexpr int SPMV_TILE = SPMV_THREADS * SPMV_PER_THREAD;   // 2048 entries per CTA
 
 // read-only load: LDG.NC where the type has an intrinsic, plain load for bool
 template <class T> __device__ __forceinline__ T ld_ro(const T *p) {
@@ -74,124 +72,232 @@ __device__ __forceinline__ int epi_store(const EpiArgs<T> &e, int64_t i, bool al
     if (!inplace) { e.wp_out[i] = w_has; if (w_has) e.w_out[i] = e.w_in[i]; }
     return w_has ? 1 : 0;
 }
+// one global atomic per CTA (every thread of the CTA must call it): same-address atomics from every warp of a
+// large grid serialise in L2 and used to cost more than the kernels themselves
+// same, with w's old state (presence, value) fetched early by the caller so the loads overlap other work
+template <class T>
+__device__ __forceinline__ int epi_store_pre(const EpiArgs<T> &e, int64_t i, bool allowed, T t, bool w_has, T w_old) {
+    if (allowed) {
+        T v = t;
+        if (e.accum >= 0 && w_has) v = binop_rt<T>(e.accum, w_old, t);
+        e.w_out[i] = v; e.wp_out[i] = 1;
+        return 1;
+    }
+    if (e.replace) { e.wp_out[i] = 0; return 0; }
+    if (e.w_out != e.w_in) { e.wp_out[i] = w_has; if (w_has) e.w_out[i] = w_old; }
+    return w_has ? 1 : 0;
+}
+// general form with everything pre-loaded (element-wise kernels batch the loads of several elements first)
+template <class T>
+__device__ __forceinline__ int epi_apply(const EpiArgs<T> &e, int64_t i, bool allowed, bool t_has, T t, bool w_has, T w_old) {
+    if (allowed) {
+        if (t_has) {
+            T v = t;
+            if (e.accum >= 0 && w_has) v = binop_rt<T>(e.accum, w_old, t);
+            e.w_out[i] = v; e.wp_out[i] = 1;
+            return 1;
+        }
+        if (e.accum < 0) { e.wp_out[i] = 0; return 0; }
+    } else if (e.replace) { e.wp_out[i] = 0; return 0; }
+    if (e.w_out != e.w_in) { e.wp_out[i] = w_has; if (w_has) e.w_out[i] = w_old; }
+    return w_has ? 1 : 0;
+}
+template <class T> __device__ __forceinline__ bool epi_needs_old(const EpiArgs<T> &e) { return e.accum >= 0 || e.w_out != e.w_in; }
+constexpr int EW_VEC = 4;            // elements per thread per pass of the element-wise kernels (loads batched)
+static inline int ew_grid4(int64_t n) { int64_t b = (n + 256 * EW_VEC - 1) / (256 * EW_VEC); return (int)(b < 1 ? 1 : b); }
 __device__ __forceinline__ void block_count_add(unsigned long long *count, int c) {
+    __shared__ int s_block_count;
+    if (count == nullptr) return;           // the caller knows the result's nvals analytically (uniform for the grid)
+    if (threadIdx.x == 0) s_block_count = 0;
+    __syncthreads();
     for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, (unsigned long long)c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_block_count, c);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_block_count) atomicAdd(count, (unsigned long long)s_block_count);
+}
+// grid size of the element-wise kernels: grid-stride loops over at most 8 CTAs per SM
+static inline int ew_grid(int64_t n) {
+    int64_t b = (n + 255) / 256;
+    if (b < 1) b = 1;
+    return (int)(b < 148 * 8 ? b : 148 * 8);
 }
 
 // ---- pull ----
+// Persistent, warp-autonomous streaming pull.  One CTA of SPMV_THREADS threads per SM; every warp walks tiles of
+// SPMV_TILE consecutive matrix entries (static round-robin), so there is no block barrier in the main loop.
+//   * the tile's indices / values are read once, fully coalesced;
+//   * gathers of u are what bounds this kernel on a power-law graph (one 32 B sector through L1TEX per lane, not
+//     HBM): the `hub_n` most frequently referenced entries of u (chosen once per matrix, grb_storage.cu:
+//     csr_ensure_hubs) are copied to shared memory at kernel start, and the matrix carries a remapped index
+//     array in which a hub column c is stored as HUB_FLAG | rank(c).  Hub lanes read shared memory and stay out
+//     of the divergent global load;
+//   * products are staged in the warp's private shared-memory strip (padded against bank conflicts); each lane
+//     reduces the rows that start in the tile, long segments are reduced by the whole warp;
+//   * rows completed inside the tile run the fused write-back w<m,replace> = accum(w, t); rows that cross tile
+//     borders leave partials in carry[] and k_spmv_fixup (one warp per tile) finishes them.
+constexpr int SPMV_THREADS = 1024;
+constexpr int SPMV_WARPS = SPMV_THREADS / 32;
+constexpr int SPMV_EPL = 8;                        // entries per lane
+constexpr int SPMV_TILE = 32 * SPMV_EPL;           // 256 entries per warp tile
+constexpr int SPMV_STRIP = SPMV_TILE + SPMV_TILE / 32;   // padded strip: index e lives at e + (e >> 5)
+constexpr int SPMV_LONG = 64;                      // segments longer than this are reduced by the whole warp
+constexpr uint32_t HUB_FLAG = 0x80000000u;
+
 template <class T> struct PullArgs {
-    const int64_t *rowptr; const uint32_t *col; const T *av; int a_iso;
+    const int64_t *rowptr; const uint32_t *col; const T *av; int a_iso;   // col: hub-remapped copy when hub_n > 0
     const T *u; const uint8_t *up;        // up == nullptr: u is full
+    const T *hub_v; const uint8_t *hub_p; int hub_n;   // compact copy of u at the hub columns (this call's values)
     int64_t nrows, nnz, ntiles;
     const int32_t *tile_row;
     T *carry_head; uint8_t *carry_head_has;   // [ntiles] partial of the row that entered the tile from the left
     T *carry_own; uint8_t *carry_own_has;     // [ntiles] partial of the tile's last owned row when it leaves the tile
     EpiArgs<T> epi;
 };
+// dynamic shared memory of k_spmv_pull for a hub table of h entries
+template <class T> static inline size_t spmv_pull_smem(int h, bool full) {
+    size_t b = (size_t)h * sizeof(T);
+    b = (b + 15) & ~(size_t)15;
+    b += (size_t)SPMV_WARPS * SPMV_STRIP * sizeof(T);
+    if (!full) b += (size_t)h + (size_t)SPMV_WARPS * SPMV_STRIP;
+    return b + 16;
+}
+template <class T> static inline int spmv_hub_capacity() {   // hub entries that fit next to the strips (both layouts)
+    const size_t budget = 216 * 1024;
+    const size_t fixed = (size_t)SPMV_WARPS * SPMV_STRIP * (sizeof(T) + 1) + 64;
+    return (int)(((budget - fixed) / (sizeof(T) + 1)) & ~(size_t)1023);
+}
+
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+template <class T> __device__ __forceinline__ T ld_stream(const T *p) {
+    if constexpr (sizeof(T) == 4) {
+        uint32_t v;
+        asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+        return *reinterpret_cast<T *>(&v);
+    } else if constexpr (sizeof(T) == 8) {
+        unsigned long long v;
+        asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p));
+        return *reinterpret_cast<T *>(&v);
+    } else return *p;
+}
 
 template <class SR>
-__global__ void __launch_bounds__(SPMV_THREADS) k_spmv_pull(PullArgs<typename SR::type> a) {
+__global__ void __launch_bounds__(SPMV_THREADS, 1) k_spmv_pull(PullArgs<typename SR::type> a) {
     using T = typename SR::type;
     using Mon = typename SR::Mon;
-    __shared__ T prod[SPMV_TILE];
-    __shared__ uint8_t flag[SPMV_TILE];
-    __shared__ int q_rows[64];
-    __shared__ int q_n;
-    const int tid = threadIdx.x;
-    const int64_t t = blockIdx.x;
-    const int64_t t0 = t * (int64_t)SPMV_TILE;
-    const int64_t t1 = (t0 + SPMV_TILE < a.nnz) ? t0 + SPMV_TILE : a.nnz;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
     const bool full = (a.up == nullptr);
-    if (tid == 0) q_n = 0;
-
-    // phase 1: coalesced stream of the tile, gather u, multiply
-    uint32_t c[SPMV_PER_THREAD];
-    T av[SPMV_PER_THREAD];
-#pragma unroll
-    for (int k = 0; k < SPMV_PER_THREAD; k++) {
-        int64_t p = t0 + k * SPMV_THREADS + tid;
-        c[k] = (p < t1) ? __ldg(a.col + p) : 0u;
-        if (SR::kUsesX && !a.a_iso) av[k] = (p < t1) ? ld_ro(a.av + p) : (T)0;
-    }
-    if (SR::kUsesX && a.a_iso) {
-        T v = a.av[0];
-#pragma unroll
-        for (int k = 0; k < SPMV_PER_THREAD; k++) av[k] = v;
-    }
-#pragma unroll
-    for (int k = 0; k < SPMV_PER_THREAD; k++) {
-        int64_t p = t0 + k * SPMV_THREADS + tid;
-        if (p < t1) {
-            T x = SR::kUsesY ? ld_ro(a.u + c[k]) : (T)0;
-            prod[k * SPMV_THREADS + tid] = SR::mult(SR::kUsesX ? av[k] : (T)0, x);
-            if (!full) flag[k * SPMV_THREADS + tid] = __ldg(a.up + c[k]);
-        }
-    }
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    T *hub = (T *)smem_raw;
+    size_t off = ((size_t)a.hub_n * sizeof(T) + 15) & ~(size_t)15;
+    T *strip = (T *)(smem_raw + off) + warp * SPMV_STRIP;
+    off += (size_t)SPMV_WARPS * SPMV_STRIP * sizeof(T);
+    uint8_t *hubp = smem_raw + off;                                   // only when !full
+    uint8_t *fstrip = hubp + a.hub_n + warp * SPMV_STRIP;             // only when !full
+    if (SR::kUsesY) for (int i = tid; i < a.hub_n; i += SPMV_THREADS) hub[i] = a.hub_v[i];
+    if (!full) for (int i = tid; i < a.hub_n; i += SPMV_THREADS) hubp[i] = a.hub_p[i];
     __syncthreads();
 
-    // phase 2: rows.  item -1 = head partial (row r_first-1 continuing from the left), items 0..nr-1 = owned rows
-    const int64_t r_first = a.tile_row[t], r_last = a.tile_row[t + 1];
-    const int nr = (int)(r_last - r_first);
-    const int64_t head_end = (r_first < a.nrows) ? a.rowptr[r_first] : a.nnz;  // entries [t0, head_end) are the head
     int my_count = 0;
-    for (int it = tid - 1; it < nr; it += SPMV_THREADS) {
-        int64_t s, e;
-        if (it < 0) { s = t0; e = head_end < t1 ? head_end : t1; if (e <= s) continue; }
-        else { s = a.rowptr[r_first + it]; e = a.rowptr[r_first + it + 1]; if (e > t1) e = t1; }
-        int len = (int)(e - s);
-        if (len > 64) {   // long segment: hand to the warps
-            int q = atomicAdd(&q_n, 1);
-            if (q < 64) { q_rows[q] = it; continue; }
+    for (int64_t t = blockIdx.x * (int64_t)SPMV_WARPS + warp; t < a.ntiles; t += (int64_t)gridDim.x * SPMV_WARPS) {
+        const int64_t t0 = t * (int64_t)SPMV_TILE;
+        const int64_t t1 = (t0 + SPMV_TILE < a.nnz) ? t0 + SPMV_TILE : a.nnz;
+        // phase 1: coalesced stream of the tile, gather u (hubs from shared memory), multiply, stage
+        uint32_t c[SPMV_EPL];
+        T av[SPMV_EPL];
+#pragma unroll
+        for (int k = 0; k < SPMV_EPL; k++) {
+            const int64_t p = t0 + k * 32 + lane;
+            c[k] = (p < t1) ? ld_stream_u32(a.col + p) : 0u;
+            if (SR::kUsesX && !a.a_iso) av[k] = (p < t1) ? ld_stream(a.av + p) : (T)0;
         }
-        T acc = Mon::identity(); bool has = false;
-        int o = (int)(s - t0);
-        for (int k = 0; k < len; k++) {
-            bool f = full || flag[o + k];
-            if (f) { acc = has ? Mon::apply(acc, prod[o + k]) : prod[o + k]; has = true; if (Mon::kAny) break; }
+        if (SR::kUsesX && a.a_iso) {
+            const T v = a.av[0];
+#pragma unroll
+            for (int k = 0; k < SPMV_EPL; k++) av[k] = v;
         }
-        if (it < 0) { a.carry_head[t] = acc; a.carry_head_has[t] = has; }
-        else {
-            int64_t r = r_first + it;
-            if (a.rowptr[r + 1] > t1) { a.carry_own[t] = acc; a.carry_own_has[t] = has; }
-            else my_count += epi_store(a.epi, r, epi_allowed(a.epi, r), has, acc);
+        T x[SPMV_EPL];
+        if (SR::kUsesY) {
+#pragma unroll
+            for (int k = 0; k < SPMV_EPL; k++) {
+                const int64_t p = t0 + k * 32 + lane;
+                x[k] = (T)0;
+                if (p < t1 && !(c[k] & HUB_FLAG)) x[k] = ld_ro(a.u + c[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < SPMV_EPL; k++)
+                if (c[k] & HUB_FLAG) x[k] = hub[c[k] & ~HUB_FLAG];
         }
-    }
-    __syncthreads();
-    // long segments: one warp each, lanes stride the segment, shuffle-reduce
-    const int nq = q_n < 64 ? q_n : 64;
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int q = warp; q < nq; q += SPMV_THREADS / 32) {
-        int it = q_rows[q];
-        int64_t s, e;
-        if (it < 0) { s = t0; e = head_end < t1 ? head_end : t1; }
-        else { s = a.rowptr[r_first + it]; e = a.rowptr[r_first + it + 1]; if (e > t1) e = t1; }
-        int len = (int)(e - s), o = (int)(s - t0);
-        T acc = Mon::identity(); bool has = false;
-        for (int k = lane; k < len; k += 32) {
-            bool f = full || flag[o + k];
-            if (f) { acc = has ? Mon::apply(acc, prod[o + k]) : prod[o + k]; has = true; }
-        }
-        for (int off = 16; off; off >>= 1) {
-            T oacc = __shfl_xor_sync(0xffffffffu, acc, off);
-            bool ohas = __shfl_xor_sync(0xffffffffu, (int)has, off) != 0;
-            if (ohas) { acc = has ? Mon::apply(acc, oacc) : oacc; has = true; }
-        }
-        if (lane == 0) {
-            if (it < 0) { a.carry_head[t] = acc; a.carry_head_has[t] = has; }
-            else {
-                int64_t r = r_first + it;
-                if (a.rowptr[r + 1] > t1) { a.carry_own[t] = acc; a.carry_own_has[t] = has; }
-                else my_count += epi_store(a.epi, r, epi_allowed(a.epi, r), has, acc);
+#pragma unroll
+        for (int k = 0; k < SPMV_EPL; k++) {
+            const int e = k * 32 + lane;
+            const int64_t p = t0 + e;
+            if (p < t1) {
+                strip[e + k] = SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0);   // e >> 5 == k
+                if (!full) fstrip[e + k] = (c[k] & HUB_FLAG) ? hubp[c[k] & ~HUB_FLAG] : __ldg(a.up + c[k]);
             }
         }
+        __syncwarp();
+
+        // phase 2: rows.  item -1 = head partial (row r_first-1 continuing from the left), items 0..nr-1 = owned rows
+        const int64_t r_first = a.tile_row[t], r_last = a.tile_row[t + 1];
+        const int nr = (int)(r_last - r_first);
+        const int64_t head_end = (r_first < a.nrows) ? a.rowptr[r_first] : a.nnz;   // entries [t0, head_end) are the head
+        for (int base = -1; base < nr; base += 32) {
+            const int it = base + lane;
+            int64_t s = 0, e = 0;
+            bool valid = it < nr;
+            if (valid) {
+                if (it < 0) { s = t0; e = head_end < t1 ? head_end : t1; valid = e > s; }
+                else { s = a.rowptr[r_first + it]; e = a.rowptr[r_first + it + 1]; if (e > t1) e = t1; }
+            }
+            const int len = (int)(e - s), o = (int)(s - t0);
+            const bool is_long = valid && len > SPMV_LONG;
+            T acc = Mon::identity(); bool has = false;
+            if (valid && !is_long) {
+                for (int k = 0; k < len; k++) {
+                    const int q = o + k, qq = q + (q >> 5);
+                    if (full || fstrip[qq]) { acc = has ? Mon::apply(acc, strip[qq]) : strip[qq]; has = true; if (Mon::kAny) break; }
+                }
+            }
+            // long segments: the whole warp strides the segment and shuffle-reduces; the owner lane keeps the result
+            unsigned lm = __ballot_sync(0xffffffffu, is_long);
+            while (lm) {
+                const int src = __ffs(lm) - 1;
+                lm &= lm - 1;
+                const int lo = __shfl_sync(0xffffffffu, o, src), ll = __shfl_sync(0xffffffffu, len, src);
+                T pacc = Mon::identity(); bool phas = false;
+                for (int k = lane; k < ll; k += 32) {
+                    const int q = lo + k, qq = q + (q >> 5);
+                    if (full || fstrip[qq]) { pacc = phas ? Mon::apply(pacc, strip[qq]) : strip[qq]; phas = true; }
+                }
+                for (int sh = 16; sh; sh >>= 1) {
+                    const T oacc = __shfl_xor_sync(0xffffffffu, pacc, sh);
+                    const bool ohas = __shfl_xor_sync(0xffffffffu, (int)phas, sh) != 0;
+                    if (ohas) { pacc = phas ? Mon::apply(pacc, oacc) : oacc; phas = true; }
+                }
+                if (lane == src) { acc = pacc; has = phas; }
+            }
+            if (valid) {
+                if (it < 0) { a.carry_head[t] = acc; a.carry_head_has[t] = has; }
+                else {
+                    const int64_t r = r_first + it;
+                    if (a.rowptr[r + 1] > t1) { a.carry_own[t] = acc; a.carry_own_has[t] = has; }
+                    else my_count += epi_store(a.epi, r, epi_allowed(a.epi, r), has, acc);
+                }
+            }
+        }
+        __syncwarp();
     }
     block_count_add(a.epi.count, my_count);
 }
 
 // one warp per tile: if the tile's last owned row runs past the tile, fold the following tiles' head partials
 template <class SR>
-__global__ void k_spmv_fixup(PullArgs<typename SR::type> a) {
+__global__ void __launch_bounds__(256) k_spmv_fixup(PullArgs<typename SR::type> a) {
     using T = typename SR::type;
     using Mon = typename SR::Mon;
     const int64_t t = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
@@ -220,6 +326,474 @@ __global__ void k_spmv_fixup(PullArgs<typename SR::type> a) {
         }
     }
     block_count_add(a.epi.count, my_count);
+}
+
+// ---- flagged-stream pull (u full): the fast path of PageRank / SSSP / FastSV iterations ----
+// Works on the cached stream form of the matrix (grb_storage.cu: csr_ensure_hubs): pcol carries, per entry, the
+// column (or 0x80000000 | hub rank) and the bit 0x40000000 on the first entry of every row; nzrow lists the rows
+// that have entries; tile_first[t] counts the rows that start before tile t.  Every lane owns 8 CONSECUTIVE
+// entries (one 256-bit load per array), reduces them in registers between row-start flags, and a 5-step
+// segmented suffix scan over the lanes closes the rows that cross lanes.  Finished row sums are compacted into
+// the warp's shared-memory strip in row order and written back, coalesced, through the fused epilogue.  A row
+// left open at the tile end is finished by its owner if it ends within the next 32 entries (one extra coalesced
+// load); longer rows leave carry_own / carry_head partials for k_stream_fixup.  About 1 warp instruction per
+// entry, against 3.3 for the staged kernel below.
+constexpr uint32_t ROW_FLAG = 0x40000000u;
+constexpr uint32_t COL_MASK = 0x3fffffffu;
+constexpr int ST_TILE = 256;
+constexpr int ST_EPL = 8;
+constexpr int ST_LOOK = 32;
+
+template <class T> struct StreamArgs {
+    const int64_t *rowptr; const uint32_t *pcol; const T *av; int a_iso;
+    const T *u;
+    const T *hub_v; int hub_n;
+    const uint32_t *nzrow; const int64_t *tile_first;
+    int64_t nrows, nnz, ntiles;
+    T *carry_head; T *carry_own;          // [ntiles]
+    int32_t *open_list; int *open_count;  // tiles whose last row stays open past the look-ahead window (k_stream_fixup)
+    EpiArgs<T> epi;
+};
+template <class T> static inline int stream_warps() { return sizeof(T) > 4 ? 16 : 32; }
+template <class T> static inline size_t stream_smem(int h) {
+    return (((size_t)h * sizeof(T) + 15) & ~(size_t)15) + (size_t)stream_warps<T>() * ST_TILE * sizeof(T) + 16;
+}
+template <class T> static inline int stream_hub_capacity() {
+    const size_t budget = 216 * 1024 - (size_t)stream_warps<T>() * ST_TILE * sizeof(T);
+    return (int)((budget / sizeof(T)) & ~(size_t)1023);
+}
+
+__device__ __forceinline__ void ld256_u32(const uint32_t *p, uint32_t (&v)[8]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]) : "l"(p));
+}
+template <class T> __device__ __forceinline__ void ld_tile_vals(const T *p, T (&v)[8]) {
+    if constexpr (sizeof(T) == 4) {
+        uint32_t r[8];
+        ld256_u32((const uint32_t *)p, r);
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = *reinterpret_cast<T *>(&r[k]);
+    } else if constexpr (sizeof(T) == 8) {
+        unsigned long long r[8];
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r[0]), "=l"(r[1]), "=l"(r[2]), "=l"(r[3]) : "l"(p));
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r[4]), "=l"(r[5]), "=l"(r[6]), "=l"(r[7]) : "l"(p + 4));
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = *reinterpret_cast<T *>(&r[k]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = p[k];
+    }
+}
+
+template <class SR, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_stream(StreamArgs<typename SR::type> a) {
+    using T = typename SR::type;
+    using Mon = typename SR::Mon;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    T *hub = (T *)smem_raw;
+    T *strip = (T *)(smem_raw + (((size_t)a.hub_n * sizeof(T) + 15) & ~(size_t)15)) + warp * ST_TILE;
+    if (SR::kUsesY) for (int i = tid; i < a.hub_n; i += WARPS * 32) hub[i] = a.hub_v[i];
+    __syncthreads();
+    const unsigned FULLM = 0xffffffffu;
+    const int e0 = lane * ST_EPL;
+    int my_count = 0;
+    const int64_t tstep = (int64_t)gridDim.x * WARPS;
+    int64_t t = blockIdx.x * (int64_t)WARPS + warp;
+    // tile_first of the current tile is fetched one tile ahead (it heads the dependent chain of the write-back)
+    int64_t tf_prev = 0, tf_cur = 0, tf_next = 0;
+    if (t < a.ntiles) { tf_prev = t > 0 ? a.tile_first[t - 1] : 0; tf_cur = a.tile_first[t]; tf_next = a.tile_first[t + 1]; }
+    for (; t < a.ntiles; t += tstep) {
+        const int64_t t0 = t * (int64_t)ST_TILE;
+        const int tl = (a.nnz - t0 < ST_TILE) ? (int)(a.nnz - t0) : ST_TILE;
+        const int64_t t1 = t0 + tl;
+        const int64_t first = tf_cur;
+        const int nrows_t = (int)(tf_next - tf_cur);
+        const bool prev_has_flag = tf_cur > tf_prev;
+        // ---- loads: 8 consecutive entries per lane; the 32-entry look-ahead goes out with them.  Entries past
+        //      the end of the matrix become one-entry dummy rows (flag + hub 0) whose sums are never emitted ----
+        uint32_t c[ST_EPL];
+        T av[ST_EPL];
+        uint32_t la_c = 0;
+        const bool la_valid = (tl == ST_TILE) && (t1 + lane < a.nnz);
+        if (tl == ST_TILE) {
+            ld256_u32(a.pcol + t0 + e0, c);
+            if (SR::kUsesX && !a.a_iso) ld_tile_vals<T>(a.av + t0 + e0, av);
+            if (la_valid) la_c = ld_stream_u32(a.pcol + t1 + lane);
+        } else {
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) {
+                const bool v = e0 + k < tl;
+                c[k] = v ? a.pcol[t0 + e0 + k] : (HUB_FLAG | ROW_FLAG);
+                if (SR::kUsesX && !a.a_iso) av[k] = v ? a.av[t0 + e0 + k] : (T)0;
+            }
+        }
+        if (SR::kUsesX && a.a_iso) {
+            const T v = a.av[0];
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) av[k] = v;
+        }
+        // the first 32 output rows of the tile: their ids, and (below) w's old state, are fetched while the
+        // stream loads are in flight, so the write-back at the end of the tile does not start a new latency chain
+        int64_t r_pre = 0;
+        if (lane < nrows_t) r_pre = a.nzrow[first + lane];
+        {   // next tile's row bookkeeping, off the critical path
+            const int64_t tn = t + tstep;
+            tf_prev = tf_cur;   // placeholder, fixed below
+            if (tn < a.ntiles) { tf_prev = a.tile_first[tn - 1]; tf_cur = a.tile_first[tn]; tf_next = a.tile_first[tn + 1]; }
+        }
+        // ---- gather (hubs from shared memory) ----
+        T x[ST_EPL];
+        if (SR::kUsesY) {
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) {
+                x[k] = (T)0;
+                if ((int)c[k] >= 0) x[k] = ld_ro(a.u + (c[k] & COL_MASK));
+            }
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) if ((int)c[k] < 0) x[k] = hub[c[k] & COL_MASK];
+        }
+        bool pre_allowed = false, pre_has = false; T pre_old = (T)0;
+        if (lane < nrows_t) {
+            pre_allowed = epi_allowed(a.epi, r_pre);
+            pre_has = a.epi.wp_in[r_pre] != 0;
+            if (a.epi.accum >= 0 || a.epi.w_out != a.epi.w_in) pre_old = a.epi.w_in[r_pre];
+        }
+        // ---- row-start flags -> slot of this lane's first row in the tile ----
+        unsigned fbits = 0;
+#pragma unroll
+        for (int k = 0; k < ST_EPL; k++) fbits |= ((c[k] >> 30) & 1u) << k;
+        const int cnt = __popc(fbits);
+        int lane_rank = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULLM, lane_rank, d); if (lane >= d) lane_rank += o; }
+        lane_rank -= cnt;
+        const unsigned flagged_lanes = __ballot_sync(FULLM, fbits != 0);
+        const bool seen = fbits != 0;
+        // ---- lane-local segmented prefix: acc[k] = sum of the entries of k's row seen so far in this lane ----
+        T acc[ST_EPL];
+        acc[0] = SR::mult(SR::kUsesX ? av[0] : (T)0, SR::kUsesY ? x[0] : (T)0);
+#pragma unroll
+        for (int k = 1; k < ST_EPL; k++) {
+            const T z = SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0);
+            acc[k] = (fbits & (1u << k)) ? z : Mon::apply(acc[k - 1], z);
+        }
+        // rows that start AND end inside the lane go straight to their slot; the part before the first flag is `head`
+        {
+            int slot = lane_rank - 1;
+#pragma unroll
+            for (int k = 1; k < ST_EPL; k++) {
+                slot += (fbits >> (k - 1)) & 1u;
+                if ((fbits & (1u << k)) && slot >= lane_rank) strip[slot] = acc[k - 1];
+            }
+        }
+        T head = acc[ST_EPL - 1];
+#pragma unroll
+        for (int k = ST_EPL - 1; k >= 1; k--) if (fbits & (1u << k)) head = acc[k - 1];
+        const bool head_has = !(fbits & 1u);
+        // ---- segmented suffix scan of the heads: S_i = head_i (+) (lane i has a row start ? nothing : S_{i+1}) ----
+        T sv = head;
+        int st = (head_has ? 1 : 0) | (seen ? 2 : 0);       // bit 0: has a value, bit 1: closed by a row start
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const T ov = __shfl_down_sync(FULLM, sv, d);
+            const int os = __shfl_down_sync(FULLM, st, d);
+            if (lane + d < 32 && !(st & 2)) {
+                if (os & 1) { sv = (st & 1) ? Mon::apply(sv, ov) : ov; st |= 1; }
+                st |= os & 2;
+            }
+        }
+        const T nv = __shfl_down_sync(FULLM, sv, 1);
+        const int ns = __shfl_down_sync(FULLM, st, 1);
+        T total = acc[ST_EPL - 1];                          // the row opened by this lane's last flag
+        if (lane < 31 && (ns & 1)) total = Mon::apply(total, nv);
+        const int last_lane = 31 - __clz(flagged_lanes);     // -1 if the tile has no row start
+        if (seen && lane != last_lane) strip[lane_rank + cnt - 1] = total;
+        // ---- tile head: the part of a row that began in an earlier tile ----
+        {
+            int head_len = tl;
+            if (flagged_lanes) {
+                const int fl = __ffs(flagged_lanes) - 1;
+                head_len = fl * ST_EPL + (__ffs(__shfl_sync(FULLM, fbits, fl)) - 1);
+            }
+            const bool owner_finishes = prev_has_flag && ((flagged_lanes && head_len < ST_LOOK) || (t0 + ST_LOOK >= a.nnz));
+            if (lane == 0 && head_len > 0 && t > 0 && !owner_finishes) a.carry_head[t] = sv;
+        }
+        // ---- the row left open at the tile end: finish it from the look-ahead window, or leave a carry ----
+        int emit = nrows_t;
+        if (flagged_lanes) {
+            bool closed = true; int f = 0;
+            if (tl == ST_TILE && t1 < a.nnz) {
+                const unsigned lm = __ballot_sync(FULLM, la_valid && (la_c & ROW_FLAG));
+                if (lm) f = __ffs(lm) - 1;
+                else if (t1 + ST_LOOK >= a.nnz) f = (int)(a.nnz - t1);
+                else closed = false;
+            }
+            if (closed && f > 0) {   // warp-uniform
+                T rem = Mon::identity(); int rhas = 0;
+                if (lane < f) {
+                    const T ra = SR::kUsesX ? a.av[a.a_iso ? 0 : t1 + lane] : (T)0;
+                    T rx = (T)0;
+                    if (SR::kUsesY) rx = ((int)la_c < 0) ? hub[la_c & COL_MASK] : ld_ro(a.u + (la_c & COL_MASK));
+                    rem = SR::mult(ra, rx); rhas = 1;
+                }
+#pragma unroll
+                for (int d = 16; d; d >>= 1) {
+                    const T ov = __shfl_xor_sync(FULLM, rem, d);
+                    const int oh = __shfl_xor_sync(FULLM, rhas, d);
+                    if (oh) { rem = rhas ? Mon::apply(rem, ov) : ov; rhas = 1; }
+                }
+                total = Mon::apply(total, rem);
+            }
+            if (lane == last_lane) {
+                if (closed) strip[lane_rank + cnt - 1] = total;
+                else { a.carry_own[t] = total; a.open_list[atomicAdd(a.open_count, 1)] = (int32_t)t; }
+            }
+            if (!closed) emit--;
+        }
+        __syncwarp();
+        // ---- fused write-back of the rows finished in this tile ----
+        if (lane < emit) my_count += epi_store_pre(a.epi, r_pre, pre_allowed, strip[lane], pre_has, pre_old);
+        for (int q = lane + 32; q < emit; q += 32) {
+            const int64_t r = a.nzrow[first + q];
+            my_count += epi_store(a.epi, r, epi_allowed(a.epi, r), true, strip[q]);
+        }
+        __syncwarp();
+    }
+    block_count_add(a.epi.count, my_count);
+}
+
+// one warp per open row (listed by the owners): carry_own of its tile (+) the heads of the tiles it runs through
+template <class SR>
+__global__ void __launch_bounds__(256) k_stream_fixup(StreamArgs<typename SR::type> a) {
+    using T = typename SR::type;
+    using Mon = typename SR::Mon;
+    const int lane = threadIdx.x & 31;
+    const int nopen = *a.open_count;
+    int my_count = 0;
+    for (int w = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5); w < nopen; w += (int)((gridDim.x * (int64_t)blockDim.x) >> 5)) {
+        const int64_t t = a.open_list[w];
+        const int64_t r = a.nzrow[a.tile_first[t + 1] - 1], rend = a.rowptr[r + 1];
+        const int64_t t_end = (rend - 1) / ST_TILE;
+        T acc = Mon::identity(); bool has = false;
+        int64_t k = t + 1 + lane;
+        for (; k + 7 * 32 <= t_end; k += 8 * 32) {     // hub rows run through thousands of tiles: 8 loads in flight
+            T v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = a.carry_head[k + j * 32];
+#pragma unroll
+            for (int j = 0; j < 8; j++) { acc = has ? Mon::apply(acc, v[j]) : v[j]; has = true; }
+        }
+        for (; k <= t_end; k += 32) { acc = has ? Mon::apply(acc, a.carry_head[k]) : a.carry_head[k]; has = true; }
+        for (int off = 16; off; off >>= 1) {
+            const T oacc = __shfl_xor_sync(0xffffffffu, acc, off);
+            const bool ohas = __shfl_xor_sync(0xffffffffu, (int)has, off) != 0;
+            if (ohas) { acc = has ? Mon::apply(acc, oacc) : oacc; has = true; }
+        }
+        if (lane == 0) {
+            acc = has ? Mon::apply(a.carry_own[t], acc) : a.carry_own[t];
+            my_count += epi_store(a.epi, r, epi_allowed(a.epi, r), true, acc);
+        }
+    }
+    block_count_add(a.epi.count, my_count);
+}
+
+// rows without entries produce no t(i): the write-back still applies (delete without accum / under replace)
+template <class T>
+__global__ void __launch_bounds__(256) k_stream_empty_rows(const int64_t *rowptr, int64_t nrows, EpiArgs<T> e) {
+    int c = 0;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x)
+        if (rowptr[r + 1] == rowptr[r]) c += epi_store(e, r, epi_allowed(e, r), false, (T)0);
+    block_count_add(e.count, c);
+}
+
+// ---- atomic-segment pull (u full, no mask, accumulator absent or equal to the monoid) ----
+// The case every iteration of PageRank (`r(plus) << A.T.mxv(w, plus_times)`), Bellman-Ford
+// (`w(min) << w.vxm(A, min_plus)`) and FastSV (`mngp << A.mxv(gp, min_second)`) hits.  Because the write-back is
+// the monoid itself, partial row sums can be combined IN the output with the monoid's atomic: every lane reduces
+// its 8 consecutive entries between row-start flags in registers and issues one reduction (RED) per row segment.
+// No staging, no warp scans, no carry / fix-up pass; two dependent memory round trips per chunk
+// (stream -> gather), the REDs are fire-and-forget.  Tiles that lie inside one hub row are pre-reduced by the warp.
+// chunk_first[i] = index in nzrow of the row that owns entry 8*i.  The caller pre-fills absent positions of w with
+// the monoid identity.  Floating-point PLUS results depend on the RED order in the last bits (north_star tolerance
+// 1e-5); integer and MIN/MAX results are exact.
+template <class T> struct RedArgs {
+    const uint32_t *pcol; const T *av; int a_iso;
+    const T *u;
+    const T *hub_v; int hub_n;
+    const uint32_t *nzrow; const uint32_t *chunk_first;
+    int64_t nnz, ntiles;
+    T *w; uint8_t *wp;            // wp == nullptr: presence is already known to be all ones
+};
+template <class T> static inline int red_warps() { return sizeof(T) > 4 ? 16 : 32; }
+// shared memory: hub table | per-warp stage (256 x (4 + sizeof(T)) bytes, filled by TMA bulk copies) | mbarriers
+template <class T> static inline size_t red_stage_bytes() { return (size_t)ST_TILE * (4 + sizeof(T)) + 128; }   // + chunk_first
+template <class T> static inline size_t red_smem(int h) {
+    return (((size_t)h * sizeof(T) + 127) & ~(size_t)127) + (size_t)red_warps<T>() * red_stage_bytes<T>() + (size_t)red_warps<T>() * 8 + 128;
+}
+template <class T> static inline int hub_capacity() {
+    const size_t budget = 224 * 1024 - (size_t)red_warps<T>() * (red_stage_bytes<T>() + 8) - 256;
+    const size_t also_stream = 216 * 1024 - (size_t)stream_warps<T>() * ST_TILE * sizeof(T);     // k_spmv_stream shares the table
+    const size_t b = budget < also_stream ? budget : also_stream;
+    return (int)((b / sizeof(T)) & ~(size_t)1023);
+}
+
+// ---- TMA bulk copy + mbarrier (sm_90+ PTX; SASS: UBLKCP / SYNCS) ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+}
+
+template <class SR, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR::type> a) {
+    using T = typename SR::type;
+    using Mon = typename SR::Mon;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr bool kStageVals = SR::kUsesX;          // iso matrices are decided at run time (a.a_iso)
+    constexpr uint32_t COL_BYTES = ST_TILE * 4, VAL_BYTES = ST_TILE * sizeof(T), CF_BYTES = 128;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    T *hub = (T *)smem_raw;
+    unsigned char *stages = smem_raw + (((size_t)a.hub_n * sizeof(T) + 127) & ~(size_t)127);
+    unsigned char *my = stages + (size_t)warp * (COL_BYTES + VAL_BYTES + CF_BYTES);
+    uint64_t *bar = (uint64_t *)(stages + (size_t)WARPS * (COL_BYTES + VAL_BYTES + CF_BYTES)) + warp;
+    const uint32_t bar_a = smem_u32(bar), col_a = smem_u32(my), val_a = col_a + COL_BYTES, cf_a = val_a + VAL_BYTES;
+    if (SR::kUsesY) for (int i = tid; i < a.hub_n; i += WARPS * 32) hub[i] = a.hub_v[i];
+    if (lane == 0) mbar_init(bar_a, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    const unsigned FULLM = 0xffffffffu;
+    const bool stage_vals = kStageVals && !a.a_iso;
+    const int64_t nfull = a.nnz / ST_TILE;             // tiles that arrive by bulk copy; a ragged last tile is loaded directly
+    const int64_t tstep = (int64_t)gridDim.x * WARPS;
+    int64_t t = blockIdx.x * (int64_t)WARPS + warp;
+    auto issue = [&](int64_t tt) {                      // lane 0: arm the barrier, start the copies of tile tt
+        mbar_expect_tx(bar_a, COL_BYTES + (stage_vals ? VAL_BYTES : 0) + CF_BYTES);
+        tma_load_1d(col_a, a.pcol + tt * ST_TILE, COL_BYTES, bar_a);
+        if (stage_vals) tma_load_1d(val_a, a.av + tt * ST_TILE, VAL_BYTES, bar_a);
+        tma_load_1d(cf_a, a.chunk_first + tt * 32, CF_BYTES, bar_a);
+    };
+    if (lane == 0 && t < nfull) issue(t);
+    uint32_t parity = 0;
+    for (; t < a.ntiles; t += tstep) {
+        const int64_t chunk = t * 32 + lane;
+        const int64_t p0 = chunk * ST_EPL;
+        const bool tile_full = t < nfull;
+        int nvalid = ST_EPL;
+        uint32_t c[ST_EPL];
+        T av[ST_EPL];
+        uint32_t j0 = 0;
+        if (tile_full) {
+            mbar_wait(bar_a, parity);
+            parity ^= 1;
+            const uint4 *pc = (const uint4 *)my + lane * 2;
+            const uint4 c0 = pc[0], c1 = pc[1];
+            c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
+            if (stage_vals) {
+                const T *pv = (const T *)(my + COL_BYTES) + lane * ST_EPL;
+#pragma unroll
+                for (int k = 0; k < ST_EPL; k++) av[k] = pv[k];
+            }
+            j0 = ((const uint32_t *)(my + COL_BYTES + VAL_BYTES))[lane];
+            __syncwarp();
+            if (lane == 0 && t + tstep < nfull) issue(t + tstep);     // next tile streams in behind the gathers
+        } else {
+            nvalid = a.nnz - p0 < 0 ? 0 : (a.nnz - p0 > ST_EPL ? ST_EPL : (int)(a.nnz - p0));
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) {
+                c[k] = (k < nvalid) ? a.pcol[p0 + k] : HUB_FLAG;      // past the end: hub 0, no flag, result unused
+                if (stage_vals) av[k] = (k < nvalid) ? a.av[p0 + k] : (T)0;
+            }
+            if (nvalid) j0 = a.chunk_first[chunk];
+        }
+        if (kStageVals && a.a_iso) {
+            const T v = a.av[0];
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) av[k] = v;
+        }
+        unsigned fbits = 0;
+#pragma unroll
+        for (int k = 0; k < ST_EPL; k++) fbits |= ((c[k] >> 30) & 1u) << k;
+        const int nseg = __popc(fbits >> 1);                 // row starts after the lane's first entry
+        // row ids of the lane's first three segments (more than three starts inside 8 entries: loaded on demand)
+        uint32_t r0 = 0, r1 = 0, r2 = 0;
+        if (nvalid) {
+            r0 = a.nzrow[j0];
+            if (nseg >= 1) r1 = a.nzrow[j0 + 1];
+            if (nseg >= 2) r2 = a.nzrow[j0 + 2];
+        }
+        T x[ST_EPL];
+        if (SR::kUsesY) {
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) {
+                x[k] = (T)0;
+                if ((int)c[k] >= 0) x[k] = ld_ro(a.u + (c[k] & COL_MASK));
+            }
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) if ((int)c[k] < 0) x[k] = hub[c[k] & COL_MASK];
+        }
+        // a tile that lies inside a single row (hub rows): one RED for the warp instead of 32 on one address
+        const uint32_t j_lane0 = __shfl_sync(FULLM, j0, 0);
+        const bool one_row = tile_full && __all_sync(FULLM, (fbits >> 1) == 0 && j0 == j_lane0);
+        T acc = SR::mult(SR::kUsesX ? av[0] : (T)0, SR::kUsesY ? x[0] : (T)0);
+        if (one_row) {
+#pragma unroll
+            for (int k = 1; k < ST_EPL; k++) acc = Mon::apply(acc, SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0));
+#pragma unroll
+            for (int d = 16; d; d >>= 1) acc = Mon::apply(acc, __shfl_xor_sync(FULLM, acc, d));
+            if (lane == 0) {
+                Mon::atomic(a.w + r0, acc);
+                if (a.wp && (fbits & 1u)) a.wp[r0] = 1;
+            }
+            continue;
+        }
+        if (nvalid == 0) continue;
+        if (a.wp && (fbits & 1u)) a.wp[r0] = 1;
+        int m = 0;
+        uint32_t r = r0;
+#pragma unroll
+        for (int k = 1; k < ST_EPL; k++) {
+            const T z = SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0);
+            if (fbits & (1u << k)) {
+                Mon::atomic(a.w + r, acc);
+                m++;
+                r = (m == 1) ? r1 : (m == 2) ? r2 : a.nzrow[j0 + m];
+                if (a.wp) a.wp[r] = 1;
+                acc = z;
+            } else if (k < nvalid) acc = Mon::apply(acc, z);
+        }
+        Mon::atomic(a.w + r, acc);
+    }
+}
+
+// w := identity where absent (accumulating call) or everywhere with presence cleared (overwriting call)
+template <class T>
+__global__ void __launch_bounds__(256) k_red_prefill(T *w, uint8_t *wp, int64_t n, T ident, int overwrite) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (overwrite) { w[i] = ident; wp[i] = 0; }
+        else if (!wp[i]) w[i] = ident;
+    }
+}
+
+template <class T>
+__global__ void k_gather_hubs(const T *u, const uint8_t *up, const uint32_t *hub_ids, int h, T *hub_v, uint8_t *hub_p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= h) return;
+    const uint32_t c = hub_ids[i];
+    hub_v[i] = u[c];
+    hub_p[i] = up ? up[c] : (uint8_t)1;
 }
 
 // ---- masked pull with early exit (ANY monoid): one thread per row, stop at the first hit ----
@@ -251,17 +825,30 @@ __global__ void __launch_bounds__(256) k_pull_any(PullArgs<typename SR::type> a)
 // ---- dense write-back w<m,replace> = accum(w, t) (after push, or when types had to be cast) ----
 template <class T>
 __global__ void __launch_bounds__(256) k_vec_writeback(EpiArgs<T> e, const T *t, const uint8_t *tp, int64_t n) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int my_count = 0;
-    if (i < n) my_count = epi_store(e, i, epi_allowed(e, i), tp[i] != 0, t[i]);
+    const bool need_old = epi_needs_old(e);
+    const int64_t base = blockIdx.x * (int64_t)(256 * EW_VEC) + threadIdx.x;
+    bool al[EW_VEC], th[EW_VEC], wh[EW_VEC]; T tv[EW_VEC], wo[EW_VEC];
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) {
+        const int64_t i = base + k * 256;
+        al[k] = th[k] = wh[k] = false; tv[k] = wo[k] = (T)0;
+        if (i < n) { al[k] = epi_allowed(e, i); th[k] = tp[i] != 0; tv[k] = t[i]; wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+    }
+#pragma unroll
+    for (int k = 0; k < EW_VEC; k++) {
+        const int64_t i = base + k * 256;
+        if (i < n) my_count += epi_apply(e, i, al[k], th[k], tv[k], wh[k], wo[k]);
+    }
     block_count_add(e.count, my_count);
 }
 
 // ---- push ----
 template <class T>
 __global__ void k_fill_identity(T *t, uint8_t *tp, int64_t n, T ident) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i < n) { t[i] = ident; tp[i] = 0; }
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        t[i] = ident; tp[i] = 0;
+    }
 }
 static __global__ void k_frontier_degrees(const uint32_t *list, int64_t nf, const int64_t *rowptr, int64_t *deg) {
     const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;

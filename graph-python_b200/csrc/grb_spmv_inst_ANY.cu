@@ -12,3 +12,15 @@ bool spmv_push_ANY(int mul, int tcode, const void *pa) {
 #undef X
     return false;
 }
+bool spmv_stream_ANY(int mul, int tcode, const void *sa) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_stream_t<Semiring<OP_ANY, OP_##MUL, CT_##TYPE>>(sa); return true; }
+    GRB_SEMIRINGS_OF_ANY(X)
+#undef X
+    return false;
+}
+bool spmv_red_ANY(int mul, int tcode, const void *ra) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_red_t<Semiring<OP_ANY, OP_##MUL, CT_##TYPE>>(ra); return true; }
+    GRB_SEMIRINGS_OF_ANY(X)
+#undef X
+    return false;
+}

@@ -12,3 +12,15 @@ bool spmv_push_PLUS(int mul, int tcode, const void *pa) {
 #undef X
     return false;
 }
+bool spmv_stream_PLUS(int mul, int tcode, const void *sa) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_stream_t<Semiring<OP_PLUS, OP_##MUL, CT_##TYPE>>(sa); return true; }
+    GRB_SEMIRINGS_OF_PLUS(X)
+#undef X
+    return false;
+}
+bool spmv_red_PLUS(int mul, int tcode, const void *ra) {
+#define X(MUL, TYPE) if (mul == OP_##MUL && tcode == TC_##TYPE) { launch_red_t<Semiring<OP_PLUS, OP_##MUL, CT_##TYPE>>(ra); return true; }
+    GRB_SEMIRINGS_OF_PLUS(X)
+#undef X
+    return false;
+}

@@ -8,10 +8,14 @@ enum PullMode { PULL_STREAM = 0, PULL_ANY = 1 };
 // args point to PullArgs<T> / PushArgs<T> of the semiring's type.  Return false if (mon, mul, type) has no kernel.
 bool spmv_launch_pull(int mon, int mul, int tcode, const void *pull_args, int mode);
 bool spmv_launch_push(int mon, int mul, int tcode, const void *push_args);
+bool spmv_launch_stream(int mon, int mul, int tcode, const void *stream_args);
+bool spmv_launch_red(int mon, int mul, int tcode, const void *red_args);         // RedArgs<T>: atomic-segment pull   // StreamArgs<T>: u full, stream form cached
 
 #define SPMV_DECL(MON)                                                                   \
     bool spmv_pull_##MON(int mul, int tcode, const void *pull_args, int mode);           \
-    bool spmv_push_##MON(int mul, int tcode, const void *push_args);
+    bool spmv_push_##MON(int mul, int tcode, const void *push_args);           \
+    bool spmv_stream_##MON(int mul, int tcode, const void *stream_args);       \
+    bool spmv_red_##MON(int mul, int tcode, const void *red_args);
 SPMV_DECL(PLUS) SPMV_DECL(MIN) SPMV_DECL(MAX) SPMV_DECL(ANY) SPMV_DECL(BOOLMON)
 #undef SPMV_DECL
 

@@ -165,9 +165,111 @@ Csr coo_to_csr(int64_t nrows, int64_t ncols, uint64_t *keys, const void *vals, b
 }
 
 // ---------------------------------------------------------------- helpers on CSR
+void csr_drop_caches(Csr &c) {
+    dfree(c.tile_row); c.tile_row = nullptr; c.ntiles = 0; c.tile_nnz = 0;
+    dfree(c.hub_ids); dfree(c.hub_col); c.hub_ids = nullptr; c.hub_col = nullptr; c.hub_n = 0; c.pull_uses = 0;
+    dfree(c.nzrow); dfree(c.tile_first); dfree(c.chunk_first); c.nzrow = nullptr; c.tile_first = nullptr; c.chunk_first = nullptr;
+    c.n_nzrow = 0; c.n_stiles = 0;
+}
 void csr_free(Csr &c) {
-    dfree(c.rowptr); dfree(c.colidx); dfree(c.vals); dfree(c.tile_row);
+    csr_drop_caches(c);
+    dfree(c.rowptr); dfree(c.colidx); dfree(c.vals);
     c = Csr();
+}
+
+// ---------------------------------------------------------------- hub cache of the pull kernel
+// The pull SpMV on a power-law graph is bound by the divergent gather of u, and a small set of columns takes a
+// large share of the references (R-MAT scale 22: the top 32 K of 4 M columns hold about half of the entries).
+// csr_ensure_hubs ranks the columns by reference count, keeps the top `capacity`, and writes a second index
+// array in which a hub column c reads 0x80000000 | rank(c); k_spmv_pull serves those from shared memory.
+__global__ void k_col_histogram(const uint32_t *col, int64_t nnz, uint32_t *count) {
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < nnz; p += (int64_t)gridDim.x * blockDim.x)
+        atomicAdd(&count[col[p]], 1u);
+}
+__global__ void k_hub_rank(const uint32_t *sorted_ids, const uint32_t *sorted_counts, int h, uint32_t *rank, uint32_t *hub_ids) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= h) return;
+    hub_ids[i] = sorted_ids[i];
+    (void)sorted_counts;
+    rank[sorted_ids[i]] = 0x80000000u | (uint32_t)i;
+}
+__global__ void k_hub_remap(const uint32_t *col, int64_t nnz, const uint32_t *rank, uint32_t *out) {
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < nnz; p += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t c = col[p], r = rank[c];
+        out[p] = r ? r : c;
+    }
+}
+struct NonEmptyRow {
+    const int64_t *rowptr;
+    __host__ __device__ bool operator()(const uint32_t &r) const { return rowptr[r + 1] > rowptr[r]; }
+};
+__global__ void k_row_start_flags(const uint32_t *nzrow, int64_t n, const int64_t *rowptr, uint32_t *pcol) {
+    const int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (j < n) pcol[rowptr[nzrow[j]]] |= 0x40000000u;
+}
+// tile_first[t] = number of non-empty rows that start before entry t*256 (t = ntiles: all of them)
+__global__ void k_tile_first(const uint32_t *nzrow, int64_t n, const int64_t *rowptr, int64_t ntiles, int64_t *tile_first) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    if (t == ntiles) { tile_first[t] = n; return; }
+    const int64_t target = t * 256;
+    int64_t lo = 0, hi = n;   // first j with rowptr[nzrow[j]] >= target
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (rowptr[nzrow[mid]] >= target) hi = mid; else lo = mid + 1; }
+    tile_first[t] = lo;
+}
+// chunk_first[i] = largest j with rowptr[nzrow[j]] <= 8 * i
+__global__ void k_chunk_first(const uint32_t *nzrow, int64_t n, const int64_t *rowptr, int64_t nchunks, uint32_t *chunk_first) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= nchunks) return;
+    const int64_t target = i * 8;
+    int64_t lo = 0, hi = n - 1;
+    while (lo < hi) { const int64_t mid = (lo + hi + 1) >> 1; if (rowptr[nzrow[mid]] <= target) lo = mid; else hi = mid - 1; }
+    chunk_first[i] = (uint32_t)lo;
+}
+void csr_ensure_hubs(Csr &c, int capacity) {
+    int h = (int)(c.ncols < capacity ? c.ncols : capacity);
+    if (h <= 0 || c.nnz == 0 || c.ncols > (int64_t)0x3fffffff || c.nrows > (int64_t)0xffffffff) return;
+    if (c.hub_col && c.hub_n <= capacity && (c.hub_n == h || c.hub_n >= capacity / 2)) return;
+    dfree(c.hub_ids); dfree(c.hub_col); c.hub_ids = nullptr; c.hub_col = nullptr; c.hub_n = 0;
+    const int64_t n = c.ncols;
+    uint32_t *count = dalloc<uint32_t>(n), *count2 = dalloc<uint32_t>(n), *ids = dalloc<uint32_t>(n), *ids2 = dalloc<uint32_t>(n);
+    dzero(count, (size_t)n * sizeof(uint32_t));
+    GRB_LAUNCH("col_histogram", k_col_histogram, 148 * 16, 256, 0, c.colidx, c.nnz, count);
+    GRB_LAUNCH("iota", k_iota_u32, nblk(n), 256, 0, ids, n);
+    cub::DoubleBuffer<uint32_t> dk(count, count2), dv(ids, ids2);
+    size_t tb = 0;
+    CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(nullptr, tb, dk, dv, n, 0, 32, g.stream));
+    void *tmp = dmalloc(tb);
+    CUDA_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tb, dk, dv, n, 0, 32, g.stream));
+    g.launches += 8;
+    dfree(tmp);
+    uint32_t *rank = dk.Alternate();   // reuse the spare key buffer as the rank table
+    dzero(rank, (size_t)n * sizeof(uint32_t));
+    c.hub_ids = dalloc<uint32_t>(h);
+    GRB_LAUNCH("hub_rank", k_hub_rank, nblk(h), 256, 0, dv.Current(), dk.Current(), h, rank, c.hub_ids);
+    c.hub_col = dalloc<uint32_t>(c.nnz);
+    GRB_LAUNCH("hub_remap", k_hub_remap, 148 * 16, 256, 0, c.colidx, c.nnz, rank, c.hub_col);
+    c.hub_n = h;
+    dfree(count); dfree(count2); dfree(ids); dfree(ids2);
+    // row structure of the flagged stream (k_spmv_stream): non-empty rows, row-start flags, rows before each tile
+    c.nzrow = dalloc<uint32_t>(c.nrows);
+    int64_t *d_n = g.d_scratch + 8;
+    NonEmptyRow pred{c.rowptr};
+    cub::CountingInputIterator<uint32_t> it(0);
+    tb = 0;
+    CUDA_TRY(cub::DeviceSelect::If(nullptr, tb, it, c.nzrow, d_n, c.nrows, pred, g.stream));
+    tmp = dmalloc(tb);
+    CUDA_TRY(cub::DeviceSelect::If(tmp, tb, it, c.nzrow, d_n, c.nrows, pred, g.stream));
+    g.launches += 1;
+    dfree(tmp);
+    c.n_nzrow = read_i64(d_n);
+    GRB_LAUNCH("row_start_flags", k_row_start_flags, nblk(c.n_nzrow), 256, 0, c.nzrow, c.n_nzrow, c.rowptr, c.hub_col);
+    c.n_stiles = cdiv(c.nnz, 256);
+    c.tile_first = dalloc<int64_t>(c.n_stiles + 1);
+    const int64_t nchunks = cdiv(c.nnz, 8);
+    c.chunk_first = dalloc<uint32_t>(nchunks);
+    GRB_LAUNCH("chunk_first", k_chunk_first, nblk(nchunks), 256, 0, c.nzrow, c.n_nzrow, c.rowptr, nchunks, c.chunk_first);
+    GRB_LAUNCH("tile_first", k_tile_first, nblk(c.n_stiles + 1), 256, 0, c.nzrow, c.n_nzrow, c.rowptr, c.n_stiles, c.tile_first);
 }
 
 uint32_t *csr_row_ids(const Csr &c) {

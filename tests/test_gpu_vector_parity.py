@@ -189,3 +189,110 @@ def test_type_mismatch_is_cast_like_c(gb):
     t = O.spmv(A, u, "PLUS", "TIMES", "FP64")
     O.vec_writeback(w, t)
     assert vec_equal(gw, w, 1e-6)
+
+
+# ---------------------------------------------------------------------------------------------- flagged-stream pull
+def _skewed_matrix(rng, n, dt):
+    """Rows of very different lengths: empty rows, length-1 rows, and hub rows spanning many 256-entry tiles."""
+    lens = rng.choice([0, 0, 1, 2, 5, 16, 40, 300, 2000], size=n, p=[.1, .1, .2, .2, .2, .1, .05, .04, .01])
+    lens = np.minimum(lens, n)
+    rows = np.repeat(np.arange(n), lens)
+    cols = np.concatenate([rng.choice(n, size=k, replace=False) for k in lens if k]) if rows.size else np.zeros(0, int)
+    if dt.startswith("FP"):
+        v = rng.random(rows.size)
+    elif dt == "BOOL":
+        v = np.ones(rows.size, dtype=bool)
+    else:
+        v = rng.integers(1, 50, size=rows.size)
+    return O.Mat.from_coo(rows, cols, v.astype(O.NP_TYPES[dt]), n, n, dt)
+
+
+@pytest.mark.parametrize("mon,mul,dt", [("PLUS", "TIMES", "FP32"), ("PLUS", "TIMES", "INT64"), ("MIN", "PLUS", "INT64"),
+                                        ("MIN", "SECOND", "UINT32"), ("PLUS", "PAIR", "INT64"), ("LOR", "LAND", "BOOL"),
+                                        ("MAX", "PLUS", "FP64"), ("PLUS", "SECOND", "FP32")])
+@pytest.mark.parametrize("hub_mode", [0, 2])
+def test_stream_pull_full_vector(gb, mon, mul, dt, hub_mode):
+    """u full -> k_spmv_stream (hub_mode 2 builds the stream form at once) vs the staged kernel (hub_mode 0) vs oracle;
+    masks, accumulators and replace through the fused epilogue; hub rows crossing tiles; empty rows."""
+    from graphblas_b200 import binary
+
+    rng = np.random.default_rng(21)
+    n = 3000
+    A = _skewed_matrix(rng, n, dt)
+    gA = to_gpu_matrix(gb, A)
+    At = A.transpose()
+    tol = FP_TOL if dt.startswith("FP") and mon == "PLUS" else None
+    gb.set_option("force_direction", 1)
+    gb.set_option("hub_mode", hub_mode)
+    try:
+        u = _rand_vec(rng, n, dt, 1.0)
+        gu = to_gpu_vector(gb, u)
+        sr = _sr(gb, mon, mul)
+        for tran in (False, True):
+            w = O.Vec.empty(n, dt)
+            O.mxv(w, A, u, mon, mul, dt, tran0=tran, At=At)
+            gw = ((gA.T if tran else gA).mxv(gu, sr)).new()
+            assert vec_equal(gw, w, tol), (tran, gb.last_kernel())
+            assert gw.nvals == w.nvals
+        m = _rand_vec(rng, n, "INT32", 0.5)
+        m.values[rng.random(n) < 0.5] = 0
+        w0 = _rand_vec(rng, n, dt, 0.6)
+        acc_name = None if dt == "BOOL" else ("MIN" if mon == "MIN" else "PLUS")
+        # no mask, accumulator == monoid (atomic-segment kernel) and != monoid (flagged-stream kernel); w partly / fully present
+        for accum in ([mon] if mon in ("PLUS", "MIN", "MAX") and dt != "BOOL" else []) + ([acc_name] if acc_name else []):
+            for dens in (0.6, 1.0):
+                wa = _rand_vec(rng, n, dt, dens)
+                w = wa.dup()
+                O.mxv(w, A, u, mon, mul, dt, accum=accum)
+                gw = to_gpu_vector(gb, wa)
+                gw(getattr(binary, accum.lower())) << gA.mxv(gu, sr)
+                assert vec_equal(gw, w, tol), (accum, dens, gb.last_kernel())
+                assert gw.nvals == w.nvals
+        for comp, structure, replace, accum in ((False, False, False, None), (True, True, True, acc_name),
+                                                (False, True, False, acc_name), (True, False, True, None)):
+            w = w0.dup()
+            O.mxv(w, A, u, mon, mul, dt, mask=m, accum=accum, replace=replace, comp=comp, structure=structure)
+            gw, gm = to_gpu_vector(gb, w0), to_gpu_vector(gb, m)
+            mask = gm.S if structure else gm.V
+            mask = ~mask if comp else mask
+            kw = dict(mask=mask, replace=replace)
+            if accum:
+                kw["accum"] = getattr(binary, accum.lower())
+            gw(**kw) << gA.mxv(gu, sr)
+            assert vec_equal(gw, w, tol), (comp, structure, replace, accum, gb.last_kernel())
+            assert gw.nvals == w.nvals
+        # w aliasing u: w(min) << w.vxm(A) ping-pong through the stream kernel
+        if dt == "INT64" and mon == "MIN":
+            w = u.dup()
+            O.vxm(w, w.dup(), A, mon, mul, dt, accum="MIN", At=At)
+            gw = to_gpu_vector(gb, u)
+            gw(binary.min) << gw.vxm(gA, sr)
+            assert vec_equal(gw, w)
+    finally:
+        gb.set_option("hub_mode", 1)
+        gb.set_option("force_direction", 0)
+
+
+def test_stream_pull_tile_edges(gb):
+    """Row boundaries on and around the 256-entry tile borders and the 32-entry look-ahead window."""
+    from graphblas_b200 import semiring
+
+    rng = np.random.default_rng(22)
+    gb.set_option("hub_mode", 2)
+    gb.set_option("force_direction", 1)
+    try:
+        for lens in ([256, 256, 1], [255, 1, 256, 31, 32, 33, 1], [200, 56 + 31, 300], [200, 56 + 32, 5], [200, 56 + 33, 5],
+                     [1] * 300, [700, 1, 1, 254, 290], [256 * 3], [3, 0, 0, 253, 0, 32], [250, 6 + 256 + 10, 20]):
+            n = max(max(lens), len(lens)) + 5
+            rows = np.repeat(np.arange(len(lens)), lens)
+            cols = np.concatenate([np.sort(rng.choice(n, size=k, replace=False)) for k in lens if k])
+            vals = rng.integers(1, 9, size=rows.size).astype(np.int64)
+            A = O.Mat.from_coo(rows, cols, vals, n, n, "INT64")
+            u = O.Vec(rng.integers(1, 9, size=n).astype(np.int64), np.ones(n, dtype=np.uint8), "INT64")
+            w = O.Vec.empty(n, "INT64")
+            O.mxv(w, A, u, "PLUS", "TIMES", "INT64")
+            gw = to_gpu_matrix(gb, A).mxv(to_gpu_vector(gb, u), semiring.plus_times).new()
+            assert vec_equal(gw, w), lens
+    finally:
+        gb.set_option("hub_mode", 1)
+        gb.set_option("force_direction", 0)
