@@ -137,6 +137,7 @@ struct GrbGlobal {
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
     int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
     int64_t burble = 0;
+    int64_t red_flags = 0;         // k_spmv_red: bit 0 = direct loads instead of TMA bulk copies (A/B measurements)
     int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
     // scratch
     int64_t *d_scratch = nullptr;  // 64 int64 of device scratch (counters)

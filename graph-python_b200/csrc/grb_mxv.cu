@@ -199,7 +199,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         ra.hub_n = M->hub_n; ra.nzrow = M->nzrow; ra.chunk_first = M->chunk_first; ra.nnz = M->nnz; ra.ntiles = M->n_stiles;
         T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
         GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, (const uint8_t *)nullptr, M->hub_ids, ra.hub_n, hv, hp);
-        ra.hub_v = hv;
+        ra.hub_v = hv; ra.flags = (int)g.red_flags;
         const T ident = monoid_identity<T>(mon);
         const bool overwrite = !fused || accum < 0;
         const bool w_full = fused && w->nvals_known && w->nvals == n_out;

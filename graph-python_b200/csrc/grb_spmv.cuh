@@ -624,6 +624,7 @@ template <class T> struct RedArgs {
     const uint32_t *nzrow; const uint32_t *chunk_first;
     int64_t nnz, ntiles;
     T *w; uint8_t *wp;            // wp == nullptr: presence is already known to be all ones
+    int flags;                    // bit 0: load tiles directly instead of by TMA (option red_flags = 1, for A/B measurements)
 };
 template <class T> static inline int red_warps() { return sizeof(T) > 4 ? 16 : 32; }
 // shared memory: hub table | per-warp stage (256 x (4 + sizeof(T)) bytes, filled by TMA bulk copies) | mbarriers
@@ -676,7 +677,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
     __syncthreads();
     const unsigned FULLM = 0xffffffffu;
     const bool stage_vals = kStageVals && !a.a_iso;
-    const int64_t nfull = a.nnz / ST_TILE;             // tiles that arrive by bulk copy; a ragged last tile is loaded directly
+    const int64_t nfull = (a.flags & 1) ? 0 : a.nnz / ST_TILE;   // tiles that arrive by bulk copy; a ragged last tile is loaded directly
     const int64_t tstep = (int64_t)gridDim.x * WARPS;
     int64_t t = blockIdx.x * (int64_t)WARPS + warp;
     auto issue = [&](int64_t tt) {                      // lane 0: arm the barrier, start the copies of tile tt
@@ -707,6 +708,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
                 for (int k = 0; k < ST_EPL; k++) av[k] = pv[k];
             }
             j0 = ((const uint32_t *)(my + COL_BYTES + VAL_BYTES))[lane];
+            // the generic-proxy reads above must be ordered before the async-proxy (TMA) writes that re-fill the stage:
+            // without this fence tiles were observed half-overwritten on B200 (tools/debug/dbg_red.py)
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0 && t + tstep < nfull) issue(t + tstep);     // next tile streams in behind the gathers
         } else {

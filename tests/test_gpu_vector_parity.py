@@ -296,3 +296,46 @@ def test_stream_pull_tile_edges(gb):
     finally:
         gb.set_option("hub_mode", 1)
         gb.set_option("force_direction", 0)
+
+
+@pytest.mark.parametrize("mon,mul,dt,vm", [("PLUS", "TIMES", "INT64", 1), ("PLUS", "TIMES", "FP32", 2), ("MIN", "PLUS", "INT64", 1),
+                                           ("MIN", "SECOND", "UINT32", 1)])
+def test_stream_pull_hubs_and_non_hubs(gb, mon, mul, dt, vm):
+    """A graph with more columns than the shared-memory hub table holds (scale 17: 131072 columns), so both the hub
+    and the global-gather lanes of k_spmv_red / k_spmv_stream run; three chained products like the PageRank loop."""
+    from graphblas_b200 import binary
+
+    scale = 17
+    n = 1 << scale
+    A = O.rmat_matrix(scale, dt, value_mode=vm)
+    gA = gb.Matrix.rmat(scale, dt, value_mode=vm)
+    At = A.transpose()
+    rng = np.random.default_rng(33)
+    tol = FP_TOL if dt.startswith("FP") else None
+    gb.set_option("force_direction", 1)
+    gb.set_option("hub_mode", 2)
+    try:
+        u = _rand_vec(rng, n, dt, 1.0)
+        if dt.startswith("FP"):
+            u.values[:] = u.values / n
+        gu = to_gpu_vector(gb, u)
+        sr = _sr(gb, mon, mul)
+        accum = mon
+        # overwrite, then accumulate (w full), with A and with A' (cached columns); masked variant through k_spmv_stream
+        w = O.Vec.empty(n, dt)
+        O.mxv(w, A, u, mon, mul, dt, tran0=True, At=At)
+        gw = gA.T.mxv(gu, sr).new()
+        assert vec_equal(gw, w, tol) and gw.nvals == w.nvals
+        for _ in range(2):
+            O.mxv(w, A, u, mon, mul, dt, accum=accum)
+            gw(getattr(binary, accum.lower())) << gA.mxv(gu, sr)
+            assert vec_equal(gw, w, tol), gb.last_kernel()
+        m = _rand_vec(rng, n, "BOOL", 0.5)
+        gm = to_gpu_vector(gb, m)
+        O.mxv(w, A, u, mon, mul, dt, mask=m, accum=accum, structure=True, tran0=True, At=At)
+        gw(gm.S, getattr(binary, accum.lower())) << gA.T.mxv(gu, sr)
+        assert vec_equal(gw, w, tol), gb.last_kernel()
+        assert gw.nvals == w.nvals
+    finally:
+        gb.set_option("hub_mode", 1)
+        gb.set_option("force_direction", 0)
