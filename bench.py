@@ -241,7 +241,10 @@ class PageRankJob:
         outdeg = (rowptr[1:] - rowptr[:-1]).to(torch.float32)
         d = outdeg / DAMPING
         d[d == 0] = 1.0
-        self.lo, self.hi = rank * n // world, (rank + 1) * n // world
+        from graphblas_b200.sharding import BlockExchange
+
+        self.ex = BlockExchange(n, rank, world)
+        self.lo, self.hi = self.ex.lo, self.ex.hi
         nb = self.hi - self.lo
         if world == 1:
             self.P, self.transposed = A, True                    # r(plus) << A.T.mxv(w): pull over the cached columns
@@ -273,7 +276,7 @@ class PageRankJob:
         for _ in range(ITERS):
             self.wb << self.r.ewise_mult(self.d, binary.truediv)
             if self.world > 1:
-                dist.all_gather_into_tensor(self.w_t, self.wb_t)
+                self.ex.all_gather(self.w_t, self.wb_t)
             self.r[:] << self.teleport
             self.r(binary.plus) << P.mxv(self.w, semiring.plus_times)
 

@@ -1,0 +1,92 @@
+"""The five BASELINE.json workloads, written the way the reference's notebooks write them (same statements, same
+operators), on top of graphblas_b200.  bench.py times them; tests/test_gpu_workloads.py checks them against
+scipy.sparse.csgraph / dense arithmetic.  Each returns (result, stats) with the work units the metric needs."""
+import numpy as np
+
+from . import binary, monoid, semiring
+from .core import Matrix, Vector
+
+
+def bfs_levels(A, source, op=None):
+    """Level BFS: `q(~v.S, replace=True) << q.vxm(A, any_pair)` (reference notebooks/Example B.1 -- Level BFS.ipynb
+    cell 8, with the north-star semiring any_pair in place of lor_land).  v[i] = 1 + distance from source."""
+    op = op or semiring.any_pair
+    n = A.nrows
+    v = Vector("INT32", n)
+    q = Vector("BOOL", n)
+    q[source] = True
+    level = 0
+    frontier_sizes = []
+    while True:
+        level += 1
+        nq = q.nvals
+        if nq == 0:
+            break
+        frontier_sizes.append(nq)
+        v(q.V)[:] << level
+        q(~v.S, replace=True) << q.vxm(A, op)
+    return v, {"levels": level - 1, "frontier_sizes": frontier_sizes}
+
+
+def pagerank(A, d_out, damping=0.85, iters=20):
+    """notebooks/Pagerank Demo.ipynb cell 9 with a fixed iteration count: w = r / d; r[:] = teleport;
+    r(plus) << A.T.mxv(w, plus_times)."""
+    n = A.nrows
+    teleport = float(np.float32((1 - damping) / n))
+    r = Vector.from_dense(np.full(n, 1.0 / n, dtype=np.float32))
+    w = Vector("FP32", n)
+    for _ in range(iters):
+        w << r.ewise_mult(d_out, binary.truediv)
+        r[:] << teleport
+        r(binary.plus) << A.T.mxv(w, semiring.plus_times)
+    return r, {"iterations": iters}
+
+
+def sssp_bellman_ford(A, source, max_iters=None):
+    """`w(min) << w.vxm(A, min_plus)` to the fixed point (notebooks/Intro to GraphBLAS + SSSP example.ipynb cell 21)."""
+    n = A.nrows
+    w = Vector(A.dtype, n)
+    w[source] = 0
+    iters = 0
+    max_iters = max_iters or n
+    while iters < max_iters:
+        prev_nvals = w.nvals
+        prev = w.dup()
+        w(binary.min) << w.vxm(A, semiring.min_plus)
+        iters += 1
+        if w.nvals == prev_nvals and w.isequal(prev):
+            break
+    return w, {"iterations": iters}
+
+
+def triangle_count(A):
+    """Sandia-LL: L = tril(A, -1); C(L.S) << L.mxm(L.T, plus_pair); sum(C) (BASELINE config 4)."""
+    L = A.select("tril", -1).new()
+    C = Matrix("INT64", A.nrows, A.ncols)
+    C(L.S) << L.mxm(L.T, semiring.plus_pair)
+    ntri = C.reduce_scalar(monoid.plus).value
+    return int(ntri or 0), {"nnz_L": L.nvals, "nnz_C": C.nvals}
+
+
+def spgemm(A, op=None):
+    """C = A (+).(x) A (BASELINE config 5a)."""
+    C = A.mxm(A, op or semiring.plus_times).new()
+    return C, {"nnz_C": C.nvals}
+
+
+def cc_min_label(A, max_iters=None):
+    """Connected components by min-label propagation with the FastSV product `mngp << A.mxv(gp, min_second)`
+    (notebooks/Connected Components -- FastSV.ipynb cell 30).  FastSV's hooking / shortcutting steps need
+    assign-by-index and extract (SURVEY 8f "next"); this loop keeps the product and the element-wise min, which is the
+    part BASELINE config 5b measures (GTEPS = iterations x nnz / time)."""
+    n = A.nrows
+    f = Vector.from_dense(np.arange(n, dtype=np.uint32))
+    iters = 0
+    max_iters = max_iters or n
+    while iters < max_iters:
+        prev = f.dup()
+        f(binary.min) << A.mxv(f, semiring.min_second)
+        iters += 1
+        if f.isequal(prev):
+            break
+    return f, {"iterations": iters}

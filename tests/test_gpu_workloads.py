@@ -1,0 +1,120 @@
+"""GPU: the five BASELINE workloads in the reference's notebook syntax (graphblas_b200/workloads.py) against
+independent CPU implementations (scipy.sparse / scipy.sparse.csgraph), the cross-library checks SURVEY 8c calls for."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+from scipy.sparse import csgraph
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+SCALE = 13
+
+
+@pytest.fixture(scope="module")
+def gb():
+    import graphblas_b200 as gb
+
+    gb.init("b200")
+    return gb
+
+
+def _scipy(A):
+    return sp.csr_matrix((A.values, A.indices, A.indptr), shape=A.shape)
+
+
+def test_level_bfs_vs_scipy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(SCALE, "BOOL", symmetrize=True)
+    gA = gb.Matrix.rmat(SCALE, "BOOL", symmetrize=True)
+    S = _scipy(A).astype(np.int8)
+    deg = np.diff(A.indptr)
+    for src in (int(np.argmax(deg)), int(np.nonzero(deg)[0][17])):
+        dist = csgraph.shortest_path(S, unweighted=True, indices=src)
+        v, st = W.bfs_levels(gA, src)
+        vals, pres = v.to_dense()
+        reach = np.isfinite(dist)
+        assert np.array_equal(pres, reach)
+        assert np.array_equal(vals[reach], (dist[reach] + 1).astype(np.int32))
+        assert st["levels"] == int(dist[reach].max()) + 1
+    # lor_land gives the same levels as any_pair (the notebook's original semiring)
+    from graphblas_b200 import semiring
+    v2, _ = W.bfs_levels(gA, src, semiring.lor_land)
+    assert v2.isequal(v)
+
+
+def test_sssp_vs_scipy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(SCALE, "INT64", symmetrize=True, value_mode=1)
+    gA = gb.Matrix.rmat(SCALE, "INT64", symmetrize=True, value_mode=1)
+    S = _scipy(A).astype(np.float64)
+    src = int(np.argmax(np.diff(A.indptr)))
+    dist = csgraph.dijkstra(S, indices=src)
+    w, st = W.sssp_bellman_ford(gA, src)
+    vals, pres = w.to_dense()
+    reach = np.isfinite(dist)
+    assert np.array_equal(pres, reach)
+    assert np.array_equal(vals[reach], dist[reach].astype(np.int64))
+    assert st["iterations"] < 64
+
+
+def test_triangle_count_vs_scipy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(11, "INT64", symmetrize=True)
+    gA = gb.Matrix.rmat(11, "INT64", symmetrize=True)
+    S = _scipy(A).astype(np.int64)
+    expect = int((S @ S @ S).diagonal().sum() // 6)
+    ntri, st = W.triangle_count(gA)
+    assert ntri == expect
+    assert st["nnz_L"] == A.nnz // 2
+
+
+def test_spgemm_vs_scipy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(12, "FP64", value_mode=2)
+    gA = gb.Matrix.rmat(12, "FP64", value_mode=2)
+    S = _scipy(A)
+    C = (S @ S).tocsr()
+    C.sort_indices()
+    gC, st = W.spgemm(gA)
+    ap, ai, ax = gC.to_csr()
+    # scipy drops nothing here (no cancellation with positive values): identical pattern, values within 1e-5 relative
+    assert st["nnz_C"] == C.nnz
+    assert np.array_equal(ap.astype(np.int64), C.indptr.astype(np.int64)) and np.array_equal(ai.astype(np.int64), C.indices.astype(np.int64))
+    assert np.allclose(ax, C.data, rtol=1e-5, atol=0)
+
+
+def test_connected_components_vs_scipy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(SCALE, "BOOL", symmetrize=True)
+    gA = gb.Matrix.rmat(SCALE, "BOOL", symmetrize=True)
+    ncomp, labels = csgraph.connected_components(_scipy(A).astype(np.int8), directed=False)
+    f, st = W.cc_min_label(gA)
+    got, _ = f.to_dense()
+    n = A.shape[0]
+    # scipy's labels are arbitrary: compare as partitions through the minimum vertex id of each component
+    mins = np.full(ncomp, n, dtype=np.int64)
+    np.minimum.at(mins, labels, np.arange(n))
+    assert np.array_equal(got.astype(np.int64), mins[labels])
+
+
+def test_pagerank_vs_numpy(gb):
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(SCALE, "FP32", value_mode=2)
+    gA = gb.Matrix.rmat(SCALE, "FP32", value_mode=2)
+    n = A.shape[0]
+    d = np.diff(A.indptr).astype(np.float32) / np.float32(0.85)
+    d[d == 0] = 1
+    r, _ = W.pagerank(gA, gb.Vector.from_dense(d), iters=10)
+    P = _scipy(A).T.tocsr().astype(np.float64)
+    x = np.full(n, 1.0 / n)
+    for _ in range(10):
+        x = (1 - 0.85) / n + P @ (x / d)
+    got, _ = r.to_dense()
+    assert np.allclose(got, x, rtol=2e-5, atol=1e-9)
