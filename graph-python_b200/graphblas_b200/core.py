@@ -585,9 +585,15 @@ class Vector(BaseType):
             return False
         if self._size != other._size or self.nvals != other.nvals:
             return False
-        i1, v1 = self.to_coo()
-        i2, v2 = other.to_coo(self.dtype)
-        return bool(np.array_equal(i1, i2) and np.array_equal(v1, v2))
+        if self.nvals == 0:
+            return True
+        # on the device, as the reference does it (core/vector.py isequal -> eWiseMult(eq) + reduce(land)):
+        # equal patterns <=> the intersection has as many entries as either operand
+        matches = Vector(dtypes.BOOL, self._size)
+        matches << self.ewise_mult(other, binary.eq)
+        if matches.nvals != self.nvals:
+            return False
+        return bool(matches.reduce(monoid.land).value)
 
     def isclose(self, other, *, rel_tol=1e-7, abs_tol=0.0, check_dtype=False):
         if self._size != other._size or self.nvals != other.nvals:
@@ -921,9 +927,14 @@ class Matrix(BaseType):
             return False
         if self.shape != other.shape or self.nvals != other.nvals:
             return False
-        r1, c1, v1 = self.to_coo()
-        r2, c2, v2 = other.to_coo(self.dtype)
-        return bool(np.array_equal(r1, r2) and np.array_equal(c1, c2) and np.array_equal(v1, v2))
+        if self.nvals == 0:
+            return True
+        # reference core/matrix.py:387-398: eWiseMult(eq) + reduce(land), all on the device
+        matches = Matrix(dtypes.BOOL, self._nrows, self._ncols)
+        matches << self.ewise_mult(other, binary.eq)
+        if matches.nvals != self.nvals:
+            return False
+        return bool(matches.reduce_scalar(monoid.land).value)
 
     def isclose(self, other, *, rel_tol=1e-7, abs_tol=0.0, check_dtype=False):
         if self.shape != other.shape or self.nvals != other.nvals:
