@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel device times of the timed region to stderr")
     ap.add_argument("--hub-mode", type=int, default=None, help="libgrb_b200 option hub_mode (0 off, 1 auto, 2 always)")
+    ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
+    ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
     return ap.parse_args()
 
@@ -391,6 +393,10 @@ def run_b200(args):
     gb.use_torch_stream()
     if args.hub_mode is not None:
         gb.set_option("hub_mode", args.hub_mode)
+    if args.red_flags:
+        gb.set_option("red_flags", args.red_flags)
+    if args.smem_kb:
+        gb.set_option("smem_kb", args.smem_kb)
     scale = args.scale + int(np.log2(world))
     job = PageRankJob(gb, scale, rank, world)
     nnz = job.nnz_total

@@ -137,6 +137,8 @@ struct GrbGlobal {
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
     int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
     int64_t burble = 0;
+    int64_t smem_kb = 194;         // shared-memory budget of the hub-table kernels: <= 195 KB keeps the 196 KB carve-out, i.e. 60 KB of L1
+                                   // for gather misses in flight (228 KB carve-out: 28 KB L1, gathers 1.5x slower, tools/microbench/gather_bench5)
     int64_t red_flags = 0;         // k_spmv_red: bit 0 = direct loads instead of TMA bulk copies (A/B measurements)
     int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
     // scratch

@@ -185,21 +185,23 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     a.hub_v = nullptr; a.hub_p = nullptr; a.hub_n = 0;
     // flagged-stream fast path: u full, and the matrix is pulled from repeatedly (iterative algorithms) so that
     // building its stream form (hub ranks, row-start flags) pays off
-    bool use_stream = !pull_any && a.up == nullptr && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
+    // (the atomic-segment form also takes a sparse u: Bellman-Ford's `w(min) << w.vxm(A, min_plus)` before w fills up)
+    const bool red_shape = !have_mask && !f.comp && (accum < 0 || accum == mon);
+    bool use_stream = !pull_any && (a.up == nullptr || red_shape) && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
     if (use_stream) {
         M->pull_uses++;
         if (g.hub_mode == 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20))) csr_ensure_hubs(*M, hub_capacity<T>());
         use_stream = M->hub_col != nullptr && M->hub_n <= hub_capacity<T>();
     }
     // ---- atomic-segment pull: no mask, and the write-back is the monoid itself (or a plain overwrite) ----
-    if (use_stream && !have_mask && !f.comp && (accum < 0 || accum == mon)) {
+    if (use_stream && red_shape) {
         const bool pingpong = fused && ((w == u) || (u_vals == w->vals));
         RedArgs<T> ra;
-        ra.pcol = M->hub_col; ra.av = (const T *)M->vals; ra.a_iso = M->iso; ra.u = (const T *)u_vals;
+        ra.pcol = M->hub_col; ra.av = (const T *)M->vals; ra.a_iso = M->iso; ra.u = (const T *)u_vals; ra.up = a.up;
         ra.hub_n = M->hub_n; ra.nzrow = M->nzrow; ra.chunk_first = M->chunk_first; ra.nnz = M->nnz; ra.ntiles = M->n_stiles;
         T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
-        GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, (const uint8_t *)nullptr, M->hub_ids, ra.hub_n, hv, hp);
-        ra.hub_v = hv; ra.flags = (int)g.red_flags;
+        GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, ra.up, M->hub_ids, ra.hub_n, hv, hp);
+        ra.hub_v = hv; ra.hub_p = hp; ra.flags = (int)g.red_flags;
         const T ident = monoid_identity<T>(mon);
         const bool overwrite = !fused || accum < 0;
         const bool w_full = fused && w->nvals_known && w->nvals == n_out;
@@ -221,8 +223,8 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         if (!ok) { dfree(t); dfree(tp); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
         if (fused) {
             if (pingpong) swap_pingpong(w);
-            if (overwrite) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
-            else if (w_full) { w->list_valid = false; }
+            if (overwrite && !ra.up) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
+            else if (!overwrite && w_full) { w->list_valid = false; }
             else { count_present(w->present, n_out, w->d_nvals); vec_set_unknown_nvals(w); }
         } else {
             writeback(t, tp);

@@ -26,6 +26,22 @@ template <class T> __device__ __forceinline__ T ld_ro(const T *p) {
     else return __ldg(p);
 }
 
+// shared-space load from a 32-bit shared address: keeps the compiler from re-deriving the shared window base
+// (S2R SR_CgaCtaId + LEA per access under register pressure, seen in the sm_100a SASS of the pull kernels)
+template <class T> __device__ __forceinline__ T lds_at(uint32_t addr) {
+    if constexpr (sizeof(T) == 1) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr)); uint8_t b = (uint8_t)v; T o; memcpy(&o, &b, 1); return o; }
+    else if constexpr (sizeof(T) == 2) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr)); T o; memcpy(&o, &v, 2); return o; }
+    else if constexpr (sizeof(T) == 4) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); T o; memcpy(&o, &v, 4); return o; }
+    else { unsigned long long v; asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr)); T o; memcpy(&o, &v, 8); return o; }
+}
+// pin a value in a register: the compiler may not rematerialise it at each use
+__device__ __forceinline__ uint32_t pinned(uint32_t x) { uint32_t y; asm volatile("mov.u32 %0, %1;" : "=r"(y) : "r"(x)); return y; }
+__device__ __forceinline__ uint4 lds128_at(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
 // ---- fused write-back ----
 template <class T> struct EpiArgs {
     T *w_out; uint8_t *wp_out;            // destination buffers (== w_in for in-place, else the ping-pong spare)
@@ -619,8 +635,8 @@ __global__ void __launch_bounds__(256) k_stream_empty_rows(const int64_t *rowptr
 // 1e-5); integer and MIN/MAX results are exact.
 template <class T> struct RedArgs {
     const uint32_t *pcol; const T *av; int a_iso;
-    const T *u;
-    const T *hub_v; int hub_n;
+    const T *u; const uint8_t *up;              // up == nullptr: u is full (dense instantiation)
+    const T *hub_v; const uint8_t *hub_p; int hub_n;
     const uint32_t *nzrow; const uint32_t *chunk_first;
     int64_t nnz, ntiles;
     T *w; uint8_t *wp;            // wp == nullptr: presence is already known to be all ones
@@ -628,13 +644,16 @@ template <class T> struct RedArgs {
 };
 template <class T> static inline int red_warps() { return sizeof(T) > 4 ? 16 : 32; }
 // shared memory: hub table | per-warp stage (256 x (4 + sizeof(T)) bytes, filled by TMA bulk copies) | mbarriers
-template <class T> static inline size_t red_stage_bytes() { return (size_t)ST_TILE * (4 + sizeof(T)) + 128; }   // + chunk_first
+template <class T> static inline size_t red_stage_bytes() { return (size_t)ST_TILE * (4 + sizeof(T)) + 128; }   // columns, values, chunk_first
+static inline size_t red_hub_bits_bytes(int h) { return ((size_t)((h + 31) / 32) * 4 + 127) & ~(size_t)127; }   // presence bitmap of the hubs
 template <class T> static inline size_t red_smem(int h) {
-    return (((size_t)h * sizeof(T) + 127) & ~(size_t)127) + (size_t)red_warps<T>() * red_stage_bytes<T>() + (size_t)red_warps<T>() * 8 + 128;
+    return (((size_t)h * sizeof(T) + 127) & ~(size_t)127) + red_hub_bits_bytes(h) + (size_t)red_warps<T>() * red_stage_bytes<T>() +
+           (size_t)red_warps<T>() * 8 + 128;
 }
 template <class T> static inline int hub_capacity() {
-    const size_t budget = 224 * 1024 - (size_t)red_warps<T>() * (red_stage_bytes<T>() + 8) - 256;
-    const size_t also_stream = 216 * 1024 - (size_t)stream_warps<T>() * ST_TILE * sizeof(T);     // k_spmv_stream shares the table
+    const size_t total = (size_t)g.smem_kb * 1024;
+    const size_t budget = (total - (size_t)red_warps<T>() * (red_stage_bytes<T>() + 8) - 512) * 8 / (8 * sizeof(T) + 1) * sizeof(T);
+    const size_t also_stream = total - 1024 - (size_t)stream_warps<T>() * ST_TILE * sizeof(T);     // k_spmv_stream shares the table
     const size_t b = budget < also_stream ? budget : also_stream;
     return (int)((b / sizeof(T)) & ~(size_t)1023);
 }
@@ -658,20 +677,35 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
 }
 
-template <class SR, int WARPS>
+// Shared-memory budget: the hub table competes with L1 for the 256 KB of each SM.  Gather misses in flight are
+// bounded by the L1 that is left (measured, tools/microbench/gather_bench5 + bench.py --smem-kb): with the 228 KB
+// carve-out (28 KB L1) the same kernel runs 1.3-1.5x slower than with <= 196 KB (60 KB L1), although the table
+// is 20% smaller.  Issuing the next tile's gathers ahead of the reduction (look-ahead) made it slower at every
+// budget for the same reason, so each warp keeps exactly one tile in flight.
+template <class SR, int WARPS, bool SPARSE>
 __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR::type> a) {
     using T = typename SR::type;
     using Mon = typename SR::Mon;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr bool kStageVals = SR::kUsesX;          // iso matrices are decided at run time (a.a_iso)
     constexpr uint32_t COL_BYTES = ST_TILE * 4, VAL_BYTES = ST_TILE * sizeof(T), CF_BYTES = 128;
+    constexpr uint32_t WSTAGE = COL_BYTES + VAL_BYTES + CF_BYTES;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const size_t hub_bytes = ((size_t)a.hub_n * sizeof(T) + 127) & ~(size_t)127;
+    const size_t bits_bytes = ((size_t)((a.hub_n + 31) / 32) * 4 + 127) & ~(size_t)127;
     T *hub = (T *)smem_raw;
-    unsigned char *stages = smem_raw + (((size_t)a.hub_n * sizeof(T) + 127) & ~(size_t)127);
-    unsigned char *my = stages + (size_t)warp * (COL_BYTES + VAL_BYTES + CF_BYTES);
-    uint64_t *bar = (uint64_t *)(stages + (size_t)WARPS * (COL_BYTES + VAL_BYTES + CF_BYTES)) + warp;
-    const uint32_t bar_a = smem_u32(bar), col_a = smem_u32(my), val_a = col_a + COL_BYTES, cf_a = val_a + VAL_BYTES;
+    uint32_t *hub_bits = (uint32_t *)(smem_raw + hub_bytes);                       // SPARSE: presence of the hubs
+    const uint32_t hub_a = pinned(smem_u32(smem_raw)), bits_a = hub_a + (uint32_t)hub_bytes;
+    const uint32_t col_a = hub_a + (uint32_t)(hub_bytes + bits_bytes) + warp * WSTAGE, val_a = col_a + COL_BYTES, cf_a = val_a + VAL_BYTES;
+    const uint32_t bar_a = hub_a + (uint32_t)(hub_bytes + bits_bytes) + WARPS * WSTAGE + warp * 8;
     if (SR::kUsesY) for (int i = tid; i < a.hub_n; i += WARPS * 32) hub[i] = a.hub_v[i];
+    if (SPARSE) {
+        const int padded = (a.hub_n + 31) & ~31;
+        for (int i = tid; i < padded; i += WARPS * 32) {
+            const unsigned word = __ballot_sync(0xffffffffu, i < a.hub_n && a.hub_p[i] != 0);
+            if (lane == 0) hub_bits[i >> 5] = word;
+        }
+    }
     if (lane == 0) mbar_init(bar_a, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -699,15 +733,20 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
         if (tile_full) {
             mbar_wait(bar_a, parity);
             parity ^= 1;
-            const uint4 *pc = (const uint4 *)my + lane * 2;
-            const uint4 c0 = pc[0], c1 = pc[1];
+            const uint4 c0 = lds128_at(col_a + lane * 32), c1 = lds128_at(col_a + lane * 32 + 16);
             c[0] = c0.x; c[1] = c0.y; c[2] = c0.z; c[3] = c0.w; c[4] = c1.x; c[5] = c1.y; c[6] = c1.z; c[7] = c1.w;
             if (stage_vals) {
-                const T *pv = (const T *)(my + COL_BYTES) + lane * ST_EPL;
+                if constexpr (sizeof(T) == 4) {
+                    const uint4 v0 = lds128_at(val_a + lane * 32), v1 = lds128_at(val_a + lane * 32 + 16);
+                    const uint32_t raw[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-                for (int k = 0; k < ST_EPL; k++) av[k] = pv[k];
+                    for (int k = 0; k < ST_EPL; k++) memcpy(&av[k], &raw[k], 4);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < ST_EPL; k++) av[k] = lds_at<T>(val_a + (lane * ST_EPL + k) * (uint32_t)sizeof(T));
+                }
             }
-            j0 = ((const uint32_t *)(my + COL_BYTES + VAL_BYTES))[lane];
+            j0 = lds_at<uint32_t>(cf_a + lane * 4);
             // the generic-proxy reads above must be ordered before the async-proxy (TMA) writes that re-fill the stage:
             // without this fence tiles were observed half-overwritten on B200 (tools/debug/dbg_red.py)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -745,40 +784,73 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
                 x[k] = (T)0;
                 if ((int)c[k] >= 0) x[k] = ld_ro(a.u + (c[k] & COL_MASK));
             }
+        }
+        unsigned pbits = (nvalid >= ST_EPL) ? 0xffu : ((1u << nvalid) - 1u);     // entries that exist AND whose u(j) is present
+        if (SPARSE) {
+            unsigned got = 0;
 #pragma unroll
-            for (int k = 0; k < ST_EPL; k++) if ((int)c[k] < 0) x[k] = hub[c[k] & COL_MASK];
+            for (int k = 0; k < ST_EPL; k++)
+                if ((int)c[k] >= 0) got |= (__ldg(a.up + (c[k] & COL_MASK)) ? 1u : 0u) << k;
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++)
+                if ((int)c[k] < 0) { const uint32_t h = c[k] & COL_MASK; got |= ((lds_at<uint32_t>(bits_a + (h >> 5) * 4) >> (h & 31)) & 1u) << k; }
+            pbits &= got;
+        }
+        if (SR::kUsesY) {
+#pragma unroll
+            for (int k = 0; k < ST_EPL; k++) if ((int)c[k] < 0) x[k] = lds_at<T>(hub_a + (c[k] & COL_MASK) * (uint32_t)sizeof(T));
         }
         // a tile that lies inside a single row (hub rows): one RED for the warp instead of 32 on one address
         const uint32_t j_lane0 = __shfl_sync(FULLM, j0, 0);
         const bool one_row = tile_full && __all_sync(FULLM, (fbits >> 1) == 0 && j0 == j_lane0);
+        // segment state: acc is meaningful iff has
         T acc = SR::mult(SR::kUsesX ? av[0] : (T)0, SR::kUsesY ? x[0] : (T)0);
+        bool has = pbits & 1u;
         if (one_row) {
 #pragma unroll
-            for (int k = 1; k < ST_EPL; k++) acc = Mon::apply(acc, SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0));
+            for (int k = 1; k < ST_EPL; k++) {
+                const T z = SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0);
+                if (!SPARSE) acc = Mon::apply(acc, z);
+                else if (pbits & (1u << k)) { acc = has ? Mon::apply(acc, z) : z; has = true; }
+            }
 #pragma unroll
-            for (int d = 16; d; d >>= 1) acc = Mon::apply(acc, __shfl_xor_sync(FULLM, acc, d));
-            if (lane == 0) {
+            for (int d = 16; d; d >>= 1) {
+                const T ov = __shfl_xor_sync(FULLM, acc, d);
+                if (!SPARSE) acc = Mon::apply(acc, ov);
+                else {
+                    const bool oh = __shfl_xor_sync(FULLM, (int)has, d) != 0;
+                    if (oh) { acc = has ? Mon::apply(acc, ov) : ov; has = true; }
+                }
+            }
+            if (lane == 0 && (!SPARSE || has)) {
                 Mon::atomic(a.w + r0, acc);
-                if (a.wp && (fbits & 1u)) a.wp[r0] = 1;
+                if (a.wp && (SPARSE || (fbits & 1u))) a.wp[r0] = 1;
             }
             continue;
         }
         if (nvalid == 0) continue;
-        if (a.wp && (fbits & 1u)) a.wp[r0] = 1;
+        if (!SPARSE && a.wp && (fbits & 1u)) a.wp[r0] = 1;
         int m = 0;
         uint32_t r = r0;
 #pragma unroll
         for (int k = 1; k < ST_EPL; k++) {
             const T z = SR::mult(SR::kUsesX ? av[k] : (T)0, SR::kUsesY ? x[k] : (T)0);
             if (fbits & (1u << k)) {
-                Mon::atomic(a.w + r, acc);
+                if (!SPARSE || has) {
+                    Mon::atomic(a.w + r, acc);
+                    if (SPARSE && a.wp) a.wp[r] = 1;
+                }
                 m++;
                 r = (m == 1) ? r1 : (m == 2) ? r2 : a.nzrow[j0 + m];
-                if (a.wp) a.wp[r] = 1;
-                acc = z;
-            } else if (k < nvalid) acc = Mon::apply(acc, z);
+                if (!SPARSE && a.wp) a.wp[r] = 1;
+                acc = z; has = (pbits >> k) & 1u;
+            } else if (!SPARSE) { if (k < nvalid) acc = Mon::apply(acc, z); }
+            else if (pbits & (1u << k)) { acc = has ? Mon::apply(acc, z) : z; has = true; }
         }
-        Mon::atomic(a.w + r, acc);
+        if (!SPARSE || has) {
+            Mon::atomic(a.w + r, acc);
+            if (SPARSE && a.wp) a.wp[r] = 1;
+        }
     }
 }
 

@@ -339,3 +339,46 @@ def test_stream_pull_hubs_and_non_hubs(gb, mon, mul, dt, vm):
     finally:
         gb.set_option("hub_mode", 1)
         gb.set_option("force_direction", 0)
+
+
+@pytest.mark.parametrize("mon,mul,dt,vm", [("MIN", "PLUS", "INT64", 1), ("PLUS", "TIMES", "FP32", 2), ("ANY", "PAIR", "BOOL", 0),
+                                           ("MAX", "FIRST", "INT32", 1)])
+@pytest.mark.parametrize("density", [0.001, 0.3, 0.97])
+def test_red_pull_sparse_vector(gb, mon, mul, dt, vm, density):
+    """k_spmv_red<SPARSE>: u has holes, so hub presence bits (shared memory) and the presence gather of non-hub
+    columns decide which products exist; rows whose products are all absent must stay absent.  Overwrite,
+    accumulate into a sparse w, and the aliased Bellman-Ford form w(accum) << w.vxm(A)."""
+    from graphblas_b200 import binary
+
+    scale = 17
+    n = 1 << scale
+    A = O.rmat_matrix(scale, dt, value_mode=vm)
+    gA = gb.Matrix.rmat(scale, dt, value_mode=vm)
+    At = A.transpose()
+    rng = np.random.default_rng(int(density * 1000) + 5)
+    tol = FP_TOL if dt.startswith("FP") else None
+    gb.set_option("force_direction", 1)
+    gb.set_option("hub_mode", 2)
+    try:
+        u = _rand_vec(rng, n, dt, density)
+        if dt.startswith("FP"):
+            u.values[:] = u.values / n
+        gu = to_gpu_vector(gb, u)
+        sr = _sr(gb, mon, mul)
+        w = O.Vec.empty(n, dt)
+        O.mxv(w, A, u, mon, mul, dt)
+        gw = gA.mxv(gu, sr).new()
+        assert vec_equal(gw, w, tol) and gw.nvals == w.nvals
+        if mon != "ANY":
+            acc = getattr(binary, mon.lower())
+            O.mxv(w, A, u, mon, mul, dt, accum=mon, tran0=True, At=At)
+            gw(acc) << gA.T.mxv(gu, sr)
+            assert vec_equal(gw, w, tol) and gw.nvals == w.nvals
+            # aliased: u(accum) << u.vxm(A)   (vxm(A) == mxv with A')
+            for _ in range(2):
+                O.vxm(u, u.dup(), A, mon, mul, dt, accum=mon, At=At)
+                gu(acc) << gu.vxm(gA, sr)
+                assert vec_equal(gu, u, tol) and gu.nvals == u.nvals
+    finally:
+        gb.set_option("hub_mode", 1)
+        gb.set_option("force_direction", 0)
