@@ -74,6 +74,8 @@ struct Csr {
     int64_t *tile_first = nullptr; // [stream tiles + 1] rows of nzrow that start before the tile
     uint32_t *chunk_first = nullptr;   // [ceil(nnz / 8)] index in nzrow of the row that owns entry 8 * i
     int64_t n_stiles = 0;
+    void *cast_vals = nullptr;     // the values in another type (semiring type != matrix type), kept across calls
+    int cast_code = -1;
 };
 
 struct GB_Object {
@@ -137,6 +139,7 @@ struct GrbGlobal {
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
     int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
     int64_t burble = 0;
+    int64_t push_edge_ratio = 4;   // push only while (edges leaving the frontier) * ratio <= nnz; beyond that the pull reads less
     int64_t smem_kb = 194;         // shared-memory budget of the hub-table kernels: <= 195 KB keeps the 196 KB carve-out, i.e. 60 KB of L1
                                    // for gather misses in flight (228 KB carve-out: 28 KB L1, gathers 1.5x slower, tools/microbench/gather_bench5)
     int64_t red_flags = 0;         // k_spmv_red: bit 0 = direct loads instead of TMA bulk copies (A/B measurements)
@@ -190,6 +193,7 @@ void csr_transpose(const Csr &a, Csr &t, size_t tsize);
 void csr_ensure_tiles(Csr &c, int tile_nnz);
 void csr_ensure_hubs(Csr &c, int capacity);               // build / rebuild the hub cache for at most `capacity` hubs
 void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)
+const void *csr_vals_as(Csr &c, int from_code, int to_code);   // c.vals, or a cached typed copy of them
 void mat_set_csr(GB_Object *o, Csr &c);                   // take ownership of c as o's CSR
 Csr csr_dup(const Csr &a, size_t tsize);
 Csr vec_as_csr_column(GB_Object *v);                      // n x 1 matrix view of a vector (copy)

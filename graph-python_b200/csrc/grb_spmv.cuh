@@ -42,6 +42,40 @@ __device__ __forceinline__ uint4 lds128_at(uint32_t addr) {
     return v;
 }
 
+// (value, presence) pairs of a sparse vector, 2 * sizeof(T) bytes each: one gather (one sector) fetches both
+template <int BYTES> struct PairBits;
+template <> struct PairBits<2> { using type = uint16_t; };
+template <> struct PairBits<4> { using type = uint32_t; };
+template <> struct PairBits<8> { using type = unsigned long long; };
+template <> struct PairBits<16> { using type = ulonglong2; };
+template <class T> using pair_bits_t = typename PairBits<2 * sizeof(T)>::type;
+template <class T> __device__ __forceinline__ pair_bits_t<T> make_pair_bits(T v, bool present) {
+    pair_bits_t<T> out;
+    unsigned char raw[2 * sizeof(T)] = {};
+    memcpy(raw, &v, sizeof(T));
+    raw[sizeof(T)] = present ? 1 : 0;
+    memcpy(&out, raw, sizeof(out));
+    return out;
+}
+template <class T> __device__ __forceinline__ bool split_pair_bits(pair_bits_t<T> p, T &v) {
+    unsigned char raw[2 * sizeof(T)];
+    memcpy(raw, &p, sizeof(p));
+    memcpy(&v, raw, sizeof(T));
+    return raw[sizeof(T)] != 0;
+}
+template <class T> __device__ __forceinline__ pair_bits_t<T> ld_pair(const pair_bits_t<T> *p) {
+    if constexpr (sizeof(T) == 8) {
+        ulonglong2 v;
+        asm volatile("ld.global.nc.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p));
+        return v;
+    } else return __ldg(p);
+}
+template <class T>
+__global__ void __launch_bounds__(256) k_pack_pairs(const T *u, const uint8_t *up, int64_t n, pair_bits_t<T> *out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = make_pair_bits<T>(u[i], up[i] != 0);
+}
+
 // ---- fused write-back ----
 template <class T> struct EpiArgs {
     T *w_out; uint8_t *wp_out;            // destination buffers (== w_in for in-place, else the ping-pong spare)
@@ -358,6 +392,7 @@ constexpr uint32_t ROW_FLAG = 0x40000000u;
 constexpr uint32_t COL_MASK = 0x3fffffffu;
 constexpr int ST_TILE = 256;
 constexpr int ST_EPL = 8;
+constexpr int RED_WARPS_8B = 24;      // 8-byte types: 24 warps x 85 registers (32 would spill, 16 leaves the LSU idle)
 constexpr int ST_LOOK = 32;
 
 template <class T> struct StreamArgs {
@@ -636,13 +671,14 @@ __global__ void __launch_bounds__(256) k_stream_empty_rows(const int64_t *rowptr
 template <class T> struct RedArgs {
     const uint32_t *pcol; const T *av; int a_iso;
     const T *u; const uint8_t *up;              // up == nullptr: u is full (dense instantiation)
+    const void *upairs;                         // sparse u: (value, presence) pairs, pair_bits_t<T>[n]
     const T *hub_v; const uint8_t *hub_p; int hub_n;
     const uint32_t *nzrow; const uint32_t *chunk_first;
     int64_t nnz, ntiles;
     T *w; uint8_t *wp;            // wp == nullptr: presence is already known to be all ones
     int flags;                    // bit 0: load tiles directly instead of by TMA (option red_flags = 1, for A/B measurements)
 };
-template <class T> static inline int red_warps() { return sizeof(T) > 4 ? 16 : 32; }
+template <class T> static inline int red_warps() { return sizeof(T) > 4 ? RED_WARPS_8B : 32; }
 // shared memory: hub table | per-warp stage (256 x (4 + sizeof(T)) bytes, filled by TMA bulk copies) | mbarriers
 template <class T> static inline size_t red_stage_bytes() { return (size_t)ST_TILE * (4 + sizeof(T)) + 128; }   // columns, values, chunk_first
 static inline size_t red_hub_bits_bytes(int h) { return ((size_t)((h + 31) / 32) * 4 + 127) & ~(size_t)127; }   // presence bitmap of the hubs
@@ -778,19 +814,26 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
             if (nseg >= 2) r2 = a.nzrow[j0 + 2];
         }
         T x[ST_EPL];
-        if (SR::kUsesY) {
+        unsigned pbits = (nvalid >= ST_EPL) ? 0xffu : ((1u << nvalid) - 1u);     // entries that exist AND whose u(j) is present
+        if (!SPARSE) {
+            if (SR::kUsesY) {
+#pragma unroll
+                for (int k = 0; k < ST_EPL; k++) {
+                    x[k] = (T)0;
+                    if ((int)c[k] >= 0) x[k] = ld_ro(a.u + (c[k] & COL_MASK));
+                }
+            }
+        } else {
+            const pair_bits_t<T> *pairs = (const pair_bits_t<T> *)a.upairs;
+            pair_bits_t<T> q[ST_EPL];
 #pragma unroll
             for (int k = 0; k < ST_EPL; k++) {
-                x[k] = (T)0;
-                if ((int)c[k] >= 0) x[k] = ld_ro(a.u + (c[k] & COL_MASK));
+                q[k] = pair_bits_t<T>{};
+                if ((int)c[k] >= 0) q[k] = ld_pair<T>(pairs + (c[k] & COL_MASK));
             }
-        }
-        unsigned pbits = (nvalid >= ST_EPL) ? 0xffu : ((1u << nvalid) - 1u);     // entries that exist AND whose u(j) is present
-        if (SPARSE) {
             unsigned got = 0;
 #pragma unroll
-            for (int k = 0; k < ST_EPL; k++)
-                if ((int)c[k] >= 0) got |= (__ldg(a.up + (c[k] & COL_MASK)) ? 1u : 0u) << k;
+            for (int k = 0; k < ST_EPL; k++) got |= (split_pair_bits<T>(q[k], x[k]) ? 1u : 0u) << k;
 #pragma unroll
             for (int k = 0; k < ST_EPL; k++)
                 if ((int)c[k] < 0) { const uint32_t h = c[k] & COL_MASK; got |= ((lds_at<uint32_t>(bits_a + (h >> 5) * 4) >> (h & 31)) & 1u) << k; }

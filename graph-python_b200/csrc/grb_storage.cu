@@ -170,6 +170,19 @@ void csr_drop_caches(Csr &c) {
     dfree(c.hub_ids); dfree(c.hub_col); c.hub_ids = nullptr; c.hub_col = nullptr; c.hub_n = 0; c.pull_uses = 0;
     dfree(c.nzrow); dfree(c.tile_first); dfree(c.chunk_first); c.nzrow = nullptr; c.tile_first = nullptr; c.chunk_first = nullptr;
     c.n_nzrow = 0; c.n_stiles = 0;
+    dfree(c.cast_vals); c.cast_vals = nullptr; c.cast_code = -1;
+}
+// Matrices are replaced, never edited in place (mat_set_csr), so a typed copy of the values stays valid for the
+// life of the Csr: BOOL adjacency x INT32 vector products cast once, not per call.
+const void *csr_vals_as(Csr &c, int from_code, int to_code) {
+    if (from_code == to_code) return c.vals;
+    if (c.cast_vals && c.cast_code == to_code) return c.cast_vals;
+    dfree(c.cast_vals);
+    const int64_t n = c.iso ? 1 : c.nnz;
+    c.cast_vals = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[to_code]);
+    cast_array(c.vals, from_code, c.cast_vals, to_code, n);
+    c.cast_code = to_code;
+    return c.cast_vals;
 }
 void csr_free(Csr &c) {
     csr_drop_caches(c);
