@@ -346,6 +346,65 @@ def measure_e2e(gb, job, args, r_dev):
             "path": "Matrix.from_csc(host uint64/f32) + Vector.from_dense x2 + 20 x [ewise_mult, assign, mxv] + to_dense"}
 
 
+def e2e_pagerank_sharded(gb, host, pinned, ex, n):
+    """One rank's share of the same job from HOST buffers: import its row block of the pull matrix (CSR, uint64
+    indices), its blocks of d and r, iterate with the all-gather of w, export its block of r."""
+    from graphblas_b200 import Matrix, Vector, binary, semiring
+
+    indptr, indices, values, d, r0 = host
+    nb = d.size
+    P = Matrix.from_csr(indptr, indices, values, nrows=nb, ncols=n)
+    dv, r = Vector.from_dense(d), Vector.from_dense(r0)
+    wb = Vector.from_dense(np.zeros(nb, dtype=np.float32))
+    w = Vector.from_dense(np.zeros(n, dtype=np.float32))
+    wb_t, w_t = vector_tensor(gb, wb), vector_tensor(gb, w)
+    teleport = float(np.float32((1 - DAMPING) / n))
+    for _ in range(ITERS):
+        wb << r.ewise_mult(dv, binary.truediv)
+        ex.all_gather(w_t, wb_t)
+        r[:] << teleport
+        r(binary.plus) << P.mxv(w, semiring.plus_times)
+    out, _ = r.to_dense(out=pinned)
+    h2d = indptr.nbytes + indices.nbytes + values.nbytes + d.nbytes + r0.nbytes
+    return out, h2d, out.nbytes
+
+
+def measure_e2e_sharded(gb, job, args):
+    """e2e at N > 1: every rank starts from pinned host copies of ITS block (exported from the device once, outside
+    the timed region); wall clock between barriers, max over ranks; bytes summed over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    ap, ai, ax = job.P.to_csr()
+    d, _ = job.d.to_dense()
+    nb, n = d.size, job.n
+    keep, host = [], []
+    for a in (ap, ai, ax, d, np.full(nb, 1.0 / n, dtype=np.float32)):
+        h, t = pinned_copy(a)
+        host.append(h), keep.append(t)
+    out_pinned, t = pinned_copy(np.zeros(nb, dtype=np.float32))
+    keep.append(t)
+    e2e_pagerank_sharded(gb, host, out_pinned, job.ex, n)       # warm-up
+    torch.cuda.synchronize()
+    steps = max(2, min(args.steps, 5))
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        out, h2d, d2h = e2e_pagerank_sharded(gb, host, out_pinned, job.ex, n)
+    torch.cuda.synchronize()
+    dist.barrier()
+    dt = (time.perf_counter() - t0) / steps
+    agg = torch.tensor([dt, float(h2d), float(d2h)], device="cuda", dtype=torch.float64)
+    mx = agg.clone()
+    dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+    dt = float(mx[0].item())
+    return {"value": ITERS * job.nnz_total / dt / 1e9, "unit": "GTEPS", "h2d_bytes_per_step": int(agg[1].item()),
+            "d2h_bytes_per_step": int(agg[2].item()), "ms_per_step": dt * 1e3, "steps": steps,
+            "path": "per rank: Matrix.from_csr(host uint64/f32 row block) + Vector.from_dense x4 + 20 x [ewise_mult, "
+                    "NCCL all-gather, assign, mxv] + to_dense; max over ranks"}
+
+
 def measure_cpu_baseline(gb, job, r_dev):
     from oracle import oracle as O
 
@@ -468,8 +527,10 @@ def run_b200(args):
             line["e2e"] = measure_e2e(gb, job, args, r_dev)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = measure_cpu_baseline(gb, job, r_dev)
-    elif rank == 0:
-        line["e2e"] = None
+    elif world > 1:
+        e2e = None if args.no_e2e else measure_e2e_sharded(gb, job, args)      # collective: every rank takes part
+        if rank == 0:
+            line["e2e"] = e2e
     if rank == 0 and world == 1 and args.extra:
         if args.breakdown:
             gb.lib.GxB_b200_kernel_time_reset()

@@ -99,6 +99,10 @@ GRB_TYPE_LIST(X)
 GRB_BINOP_LIST(X)
 #undef X
 
+#define X(SYM, OP, T) static GB_UnaryOp_opaque obj_##SYM = {UOP_##OP, TCODE_##T, #SYM}; GrB_UnaryOp SYM = &obj_##SYM;
+GRB_UNOP_LIST(X)
+#undef X
+
 #define X(SYM, MON, T) static GB_Monoid_opaque obj_##SYM = {OP_##MON, TCODE_##T, #SYM}; GrB_Monoid SYM = &obj_##SYM;
 GRB_MONOID_LIST(X)
 #undef X

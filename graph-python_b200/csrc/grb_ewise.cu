@@ -36,8 +36,8 @@ static void check_vec(GB_Object *o, const char *what) {
 }
 
 // w<m,replace> = accum(w, t) where t (values of type tcode + presence) is cast to w's type if needed
-static void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f, int accum, const void *t, int tcode,
-                              const uint8_t *tp) {
+void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f, int accum, const void *t, int tcode,
+                       const uint8_t *tp) {
     int64_t n = w->nrows;
     int wcode = w->type->code;
     void *tc = nullptr;
@@ -424,7 +424,11 @@ GrB_Info GrB_Vector_assign(GrB_Vector w_, const GrB_Vector mask_, const GrB_Bina
     GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u");
     GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
     check_vec(w, "w"); check_vec(u, "u");
-    if (I != GrB_ALL) grb_throw(GrB_NOT_IMPLEMENTED, "vector assign supports GrB_ALL only");
+    if (I != GrB_ALL) {
+        if (I == nullptr) grb_throw(GrB_NULL_POINTER, "index list is NULL");
+        vector_assign_indexed(w, mask, accum_code(accum), u, I, (int64_t)ni, desc_flags(desc));
+        return GrB_SUCCESS;
+    }
     if (u->nrows != w->nrows || (mask && mask->nrows != w->nrows)) grb_throw(GrB_DIMENSION_MISMATCH, "assign: sizes differ");
     vec_writeback_any(w, mask, desc_flags(desc), accum_code(accum), u->vals, u->type->code, u->present);
     API_END(w_)

@@ -35,6 +35,7 @@ enum ObjKind { K_SCALAR = 0, K_VECTOR = 1, K_MATRIX = 2 };
 static const size_t kTypeSize[TC_COUNT] = {1, 1, 2, 4, 8, 1, 2, 4, 8, 4, 8};
 
 struct GB_Type_opaque { int code; size_t size; const char *name; };
+enum UnaryCode { UOP_IDENTITY = 0, UOP_AINV, UOP_MINV, UOP_ABS, UOP_ONE, UOP_BNOT, UOP_LNOT };
 struct GB_UnaryOp_opaque { int op; int tcode; const char *name; };
 struct GB_IndexUnaryOp_opaque { int op; const char *name; };
 struct GB_BinaryOp_opaque { int op; int xcode; int zcode; const char *name; };
@@ -186,6 +187,11 @@ void obj_invalidate_caches(GB_Object *o);                 // after the CSR chang
 void vec_alloc(GB_Object *o);                             // allocate dense storage (zeroed presence)
 void vec_ensure_alt(GB_Object *o);
 int64_t vec_nvals(GB_Object *o);                          // syncs if the count is still on the device
+struct DescFlags;
+void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f, int accum, const void *t, int tcode,
+                       const uint8_t *tp);                 // w<m,replace> = accum(w, t), t cast to w's type (grb_ewise.cu)
+void vector_assign_indexed(GB_Object *w, GB_Object *mask, int accum, GB_Object *u, const uint64_t *I, int64_t ni,
+                           const DescFlags &f);            // w<m>(I) = accum(w(I), u)  (grb_vecops.cu)
 void vec_set_unknown_nvals(GB_Object *o);                 // producer kernels wrote d_nvals
 void vec_build_list(GB_Object *o);                        // dense -> sorted index list (device compaction)
 void mat_ensure_csc(GB_Object *o);                        // build + cache the transpose on the device

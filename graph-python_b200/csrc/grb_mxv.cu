@@ -383,4 +383,42 @@ GrB_Info GrB_vxm(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, 
     API_END(w)
 }
 
+// w<m> = accum(w, (+)_j A(i,j)): the row-wise reduce of the reference's aggregators (graphblas/core/operator/agg.py)
+// is the product A (+).first 1 -- the multiply ignores the vector, so nothing is gathered and the pull kernels
+// run as a pure stream.  BOOL monoids use their GrB semiring with the multiply's neutral element instead.
+GrB_Info GrB_Matrix_reduce_Monoid(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Monoid monoid,
+                                  const GrB_Matrix A, const GrB_Descriptor desc) {
+    GrB_Vector ones = nullptr;
+    API_BEGIN
+    require_init();
+    if (!monoid) grb_throw(GrB_NULL_POINTER, "monoid is NULL");
+    GB_Object *W = obj_check(w, "w"), *Aobj = obj_check_lazy(A, "A");
+    GB_Object *M = mask ? obj_check(mask, "mask") : nullptr;
+    if (Aobj->kind != K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "A must be a matrix");
+    const DescFlags f = desc_flags(desc);
+    const int tcode = monoid->tcode;
+    GB_Semiring_opaque sr = {monoid->op, OP_FIRST, tcode, "reduce_rowwise"};
+    bool fill = true;
+    if (tcode == TC_BOOL) {
+        switch (monoid->op) {
+            case OP_LOR: sr.mul = OP_LAND; fill = true; break;
+            case OP_LXOR: sr.mul = OP_LAND; fill = true; break;
+            case OP_LAND: sr.mul = OP_LOR; fill = false; break;
+            case OP_LXNOR: sr.mul = OP_LOR; fill = false; break;
+            default: break;      // ANY_FIRST exists
+        }
+    }
+    const GrB_Index n = f.tran0 ? Aobj->nrows : Aobj->ncols;
+    static const GrB_Type types[TC_COUNT] = {GrB_BOOL, GrB_INT8, GrB_INT16, GrB_INT32, GrB_INT64, GrB_UINT8,
+                                             GrB_UINT16, GrB_UINT32, GrB_UINT64, GrB_FP32, GrB_FP64};
+    GrB_Info info = GrB_Vector_new(&ones, types[tcode], n);
+    if (info == GrB_SUCCESS) info = GrB_Vector_assign_BOOL(ones, nullptr, nullptr, fill, GrB_ALL, n, nullptr);
+    if (info != GrB_SUCCESS) grb_throw(info, "reduce: cannot build the operand vector");
+    try {
+        vector_product(W, M, accum, &sr, Aobj, (GB_Object *)ones, f, false);
+    } catch (...) { GrB_Vector_free(&ones); throw; }
+    GrB_Vector_free(&ones);
+    API_END(w)
+}
+
 }  // extern "C"

@@ -41,7 +41,7 @@ from grb_b200.errors import (  # noqa: E402,F401
     OutputNotEmpty, Panic, UninitializedObject)
 
 from . import dtypes  # noqa: E402
-from .operators import binary, monoid, semiring  # noqa: E402
+from .operators import binary, monoid, semiring, unary  # noqa: E402
 from .core import Matrix, Scalar, TransposedMatrix, Vector, replace  # noqa: E402
 
 

@@ -19,7 +19,7 @@ from grb_b200 import errors, ffi, lib
 
 from . import dtypes
 from .dtypes import lookup_dtype, unify
-from .operators import Op, TypedOp, binary, binary_from_string, get_typed_op, monoid, semiring
+from .operators import Op, TypedOp, binary, binary_from_string, get_typed_op, monoid, semiring, unary
 
 NULL = ffi.NULL
 replace = object()  # sentinel usable positionally: C(mask, replace) << ...
@@ -605,6 +605,8 @@ class Vector(BaseType):
     def __getitem__(self, key):
         if isinstance(key, slice) and key == slice(None):
             return _Assigner(Updater(self), key)
+        if isinstance(key, (list, tuple, np.ndarray)):
+            return _IndexedVector(self, _np_index(key))
         out = ffi.new(f"{_CTYPE[self.dtype.name]}*")
         info = call(f"GrB_Vector_extractElement_{self.dtype.name}", [out, self, int(key)])
         s = Scalar(self.dtype)
@@ -613,7 +615,7 @@ class Vector(BaseType):
         return _ScalarResult(s)
 
     def __setitem__(self, key, value):
-        if isinstance(key, slice) and key == slice(None):
+        if (isinstance(key, slice) and key == slice(None)) or isinstance(key, (list, tuple, np.ndarray)):
             self._assign(key, value, opts={})
         else:
             call(f"GrB_Vector_setElement_{self.dtype.name}", [self, self.dtype.np_type.type(value).item(), int(key)])
@@ -655,19 +657,28 @@ class Vector(BaseType):
 
     # ---- loop-body operations around the products ----
     def _assign(self, key, value, mask=None, accum=None, replace_=False, *, opts):
-        if not (isinstance(key, slice) and key == slice(None)):
-            raise NotImplementedError("only w[:] assignment is supported")
+        """w(mask, accum)[I] << value  ->  GrB_Vector_assign / GrB_Vector_assign_<T> (reference core/vector.py:1772-1950);
+        I is `:` (GrB_ALL) or an index list."""
+        if isinstance(key, slice) and key == slice(None):
+            I, ni, keep = lib.GrB_ALL, self._size, None
+        elif isinstance(key, (list, tuple, np.ndarray)):
+            keep = _np_index(key)
+            I, ni = _buf(keep, "GrB_Index*"), keep.size
+        else:
+            raise NotImplementedError("assignment takes w[:] or w[index list]")
         comp = structure = False
         if mask is not None:
             comp, structure = mask.complement, mask.structure
         desc = _descriptor(replace_, comp, structure, **opts)
         if isinstance(value, Scalar):
             value = value.value
+        if isinstance(value, Expression):
+            value = value.new()
         if isinstance(value, Vector):
-            call("GrB_Vector_assign", [self, mask, accum, value, lib.GrB_ALL, self._size, desc])
+            call("GrB_Vector_assign", [self, mask, accum, value, I, ni, desc])
         else:
             call(f"GrB_Vector_assign_{self.dtype.name}",
-                 [self, mask, accum, self.dtype.np_type.type(value).item(), lib.GrB_ALL, self._size, desc])
+                 [self, mask, accum, self.dtype.np_type.type(value).item(), I, ni, desc])
 
     def ewise_mult(self, other, op=binary.times):
         op = _binary_for(op, self, other)
@@ -678,6 +689,13 @@ class Vector(BaseType):
         return Expression("ewise_add", "GrB_Vector_eWiseAdd_BinaryOp", [self, other], op, Vector, (self._size,))
 
     def apply(self, op, right=None):
+        """apply(unary) -> GrB_Vector_apply; apply(binary, right=scalar) -> GrB_Vector_apply_BinaryOp2nd_<T>
+        (reference core/vector.py:1308-1420)."""
+        if right is None:
+            op = get_typed_op(op, self.dtype, kind="unary")
+            if op.opclass != "UnaryOp":
+                raise TypeError("apply with a binary operator needs right=<scalar>")
+            return Expression("apply", "GrB_Vector_apply", [self], op, Vector, (self._size,))
         op = get_typed_op(op, self.dtype, kind="binary")
         if op.opclass == "Monoid":
             op = op.parent.binaryop[op.dtype]
@@ -691,6 +709,22 @@ class Vector(BaseType):
 
     def __repr__(self):
         return f"Vector(dtype={self.dtype}, size={self._size}, nvals={self.nvals})"
+
+
+class _IndexedVector(Expression):
+    """u[I]: extract as an expression (`w << u[I]`, `u[I].new()`), or the target of an indexed assignment
+    (`u[I] << v`, `u(mask, accum)[I] << v`)."""
+
+    def __init__(self, src, index):
+        super().__init__("extract", "GrB_Vector_extract", [src], None, Vector, (index.size,),
+                         scalar_args=(_buf(index, "GrB_Index*"), index.size))
+        self._src, self._index = src, index
+
+    def __lshift__(self, value):
+        self._src._assign(self._index, value, opts={})
+
+    def update(self, value):
+        self._src._assign(self._index, value, opts={})
 
 
 class _ScalarResult:
@@ -1000,6 +1034,17 @@ class Matrix(BaseType):
         return _Materialized(result)
 
     # ---- helpers around the products ----
+    def reduce_rowwise(self, op=monoid.plus):
+        """w(i) = (+)_j A(i,j) -> GrB_Matrix_reduce_Monoid (reference core/matrix.py:2754+, aggregators agg.py:303-321)."""
+        op = get_typed_op(op, self.dtype, kind="monoid")
+        return Expression("reduce_rowwise", "GrB_Matrix_reduce_Monoid", [self], op, Vector, (self.nrows,),
+                          at=self._is_transposed)
+
+    def reduce_columnwise(self, op=monoid.plus):
+        op = get_typed_op(op, self.dtype, kind="monoid")
+        return Expression("reduce_columnwise", "GrB_Matrix_reduce_Monoid", [self], op, Vector, (self.ncols,),
+                          at=not self._is_transposed)
+
     def reduce_scalar(self, op=monoid.plus):
         op = get_typed_op(op, self.dtype, kind="monoid")
         return _ReduceExpr(self, op, "Matrix")
@@ -1072,6 +1117,8 @@ class TransposedMatrix:
     mxm = Matrix.mxm
     power = Matrix.power
     select = Matrix.select
+    reduce_rowwise = Matrix.reduce_rowwise
+    reduce_columnwise = Matrix.reduce_columnwise
     __matmul__ = BaseType.__matmul__
 
     def __repr__(self):

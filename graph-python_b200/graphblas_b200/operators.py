@@ -23,6 +23,7 @@ _MONOID_RES = [
 _BINARY_RES = [
     re.compile(rf"^G[rx]B_(FIRST|SECOND|ONEB|PAIR|ANY|PLUS|MINUS|TIMES|DIV|MIN|MAX|EQ|NE|GT|LT|GE|LE)_({_TYPES})$"),
 ]
+_UNARY_RES = [re.compile(rf"^G[rx]B_(IDENTITY|AINV|MINV|ABS|ONE|BNOT)_({_TYPES})$")]
 _BOOL_BINARY = {"GrB_LOR": "lor", "GrB_LAND": "land", "GrB_LXOR": "lxor", "GrB_LXNOR": "lxnor"}
 
 
@@ -89,6 +90,10 @@ class BinaryOp(Op):
     opclass = "BinaryOp"
 
 
+class UnaryOp(Op):
+    opclass = "UnaryOp"
+
+
 class Monoid(Op):
     opclass = "Monoid"
 
@@ -109,6 +114,7 @@ class Semiring(Op):
         return expr._with_op(_typed or self)
 
 
+unary = types.SimpleNamespace()
 binary = types.SimpleNamespace()
 monoid = types.SimpleNamespace()
 semiring = types.SimpleNamespace()
@@ -151,6 +157,13 @@ def _initialize():
                 else:
                     if sym in _BOOL_BINARY:
                         _get(binary, BinaryOp, _BOOL_BINARY[sym])._add(dtypes.BOOL, sym)
+                    elif sym == "GrB_LNOT":
+                        _get(unary, UnaryOp, "lnot")._add(dtypes.BOOL, sym)
+                    else:
+                        m = _UNARY_RES[0].match(sym)
+                        if m:
+                            op, t = m.groups()
+                            _get(unary, UnaryOp, op.lower())._add(dtypes.lookup_dtype(t), sym)
     # on BOOL, plus/times/min/max are lor/land/land/lor (C API table of built-in operators); alias them so
     # semiring.plus_times[bool] style lookups resolve the way the reference's coercion tables do
     # (reference graphblas/core/operator/semiring.py:391-510)
@@ -201,7 +214,7 @@ def get_typed_op(op, dtype, dtype2=None, *, kind):
     if isinstance(op, TypedOp):
         return op
     if isinstance(op, str):
-        ns = {"binary": binary, "monoid": monoid, "semiring": semiring}[kind]
+        ns = {"unary": unary, "binary": binary, "monoid": monoid, "semiring": semiring}[kind]
         op = binary_from_string(op) if kind == "binary" else getattr(ns, op)
     if not isinstance(op, Op):
         raise TypeError(f"Invalid operator: {op!r}")

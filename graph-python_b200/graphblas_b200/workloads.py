@@ -4,7 +4,7 @@ scipy.sparse.csgraph / dense arithmetic.  Each returns (result, stats) with the 
 import numpy as np
 
 from . import binary, monoid, semiring
-from .core import Matrix, Vector
+from .core import Matrix, Scalar, Vector
 
 
 def bfs_levels(A, source, op=None):
@@ -89,4 +89,36 @@ def cc_min_label(A, max_iters=None):
         iters += 1
         if f.isequal(prev):
             break
+    return f, {"iterations": iters}
+
+
+def fastsv(A, max_iters=None):
+    """Connected components by FastSV, statement for statement the reference's
+    notebooks/Connected Components -- FastSV.ipynb cell 30 (hooking through an indexed min-assign with duplicate
+    indices, shortcutting, grandparents by extract).  f[i] = smallest vertex id of i's component."""
+    n = A.nrows
+    I = np.arange(n)
+    dt = "UINT32" if n < (1 << 32) else "UINT64"
+    f = Vector.from_coo(I, I.astype(dt.lower()), size=n, dtype=dt)   # the parent of each vertex is the vertex itself
+    gp = f.dup()              # grandparents
+    gp_dup = gp.dup()
+    mngp = f.dup()            # minimum grandparent of each star vertex
+    mod = Vector("BOOL", n)
+    change = True
+    iters = 0
+    while change and (max_iters is None or iters < max_iters):
+        # Step 1: hooking
+        mngp << A.mxv(gp, semiring.min_second)
+        f(binary.min)[I] << mngp
+        f << f.ewise_add(mngp, binary.min)
+        # Step 2: shortcutting
+        f << f.ewise_add(gp, binary.min)
+        # Step 3: grandparents
+        _, I = f.to_coo()
+        gp << f[I]
+        # termination
+        mod << gp_dup.ewise_mult(gp, binary.ne)
+        change = bool(mod.reduce(monoid.lor).value)
+        gp_dup << gp
+        iters += 1
     return f, {"iterations": iters}

@@ -118,3 +118,34 @@ def test_pagerank_vs_numpy(gb):
         x = (1 - 0.85) / n + P @ (x / d)
     got, _ = r.to_dense()
     assert np.allclose(got, x, rtol=2e-5, atol=1e-9)
+
+
+def test_fastsv_vs_scipy_and_permutation(gb):
+    """The notebook's own FastSV loop (cell 30) against scipy's components, and its permutation-invariance check
+    (cells 54-55, 63): relabelling the vertices must give the same partition."""
+    from graphblas_b200 import workloads as W
+
+    A = O.rmat_matrix(SCALE, "BOOL", symmetrize=True)
+    S = _scipy(A).astype(np.int8)
+    n = A.shape[0]
+    ncomp, labels = csgraph.connected_components(S, directed=False)
+    ref = np.full(ncomp, n, dtype=np.int64)
+    np.minimum.at(ref, labels, np.arange(n))
+    gA = gb.Matrix.rmat(SCALE, "BOOL", symmetrize=True)
+    f, st = W.fastsv(gA)
+    vals, pres = f.to_dense()
+    assert pres.all()
+    assert np.array_equal(vals.astype(np.int64), ref[labels])
+    assert st["iterations"] <= 12
+    # permuted copy of the graph
+    rng = np.random.default_rng(4)
+    p = rng.permutation(n)
+    coo = S.tocoo()
+    gP = gb.Matrix.from_coo(p[coo.row], p[coo.col], np.ones(coo.nnz, dtype=bool), nrows=n, ncols=n, dup_op="lor")
+    fp, _ = W.fastsv(gP)
+    vp, _ = fp.to_dense()
+    same = vals[coo.row] == vals[coo.col]
+    assert same.all()
+    # two vertices share a label before the permutation iff they share one after it
+    a, b = rng.integers(0, n, size=20000), rng.integers(0, n, size=20000)
+    assert np.array_equal(vals[a] == vals[b], vp[p[a]] == vp[p[b]])

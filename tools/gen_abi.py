@@ -105,6 +105,21 @@ def all_monoids():
     return out
 
 
+UNOPS_T = [("IDENTITY", "GrB"), ("AINV", "GrB"), ("MINV", "GrB"), ("ABS", "GrB"), ("ONE", "GxB")]
+
+
+def all_unops():
+    out = []  # (symbol, OP, type)
+    for op, pre in UNOPS_T:
+        for t, _, _ in TYPES:
+            out.append((f"{pre}_{op}_{t}", op, t))
+    for t, _, _ in TYPES:
+        if "INT" in t:
+            out.append((f"GrB_BNOT_{t}", "BNOT", t))
+    out.append(("GrB_LNOT", "LNOT", "BOOL"))
+    return out
+
+
 def all_binops():
     out = []  # (symbol, OP, xtype, ztype)
     for op, pre in BINOPS_T:
@@ -186,6 +201,14 @@ typedef enum {
     GxB_DEFAULT = 0, GrB_REPLACE = 1, GrB_COMP = 2, GrB_TRAN = 3, GrB_STRUCTURE = 4,
     GxB_AxB_GUSTAVSON = 1001, GxB_AxB_DOT = 1003, GxB_AxB_HASH = 1004, GxB_AxB_SAXPY = 1005
 } GrB_Desc_Value;
+
+/* object / global options queried by the reference (graphblas/__init__.py:158, core/ss/matrix.py:216-220) */
+typedef enum {
+    GxB_HYPER_SWITCH = 0, GxB_FORMAT = 1, GxB_MODE = 2, GxB_SPARSITY_CONTROL = 32, GxB_SPARSITY_STATUS = 33,
+    GxB_BITMAP_SWITCH = 34
+} GxB_Option_Field;
+typedef enum { GxB_BY_ROW = 0, GxB_BY_COL = 1 } GxB_Format_Value;
+enum { GxB_HYPERSPARSE = 1, GxB_SPARSE = 2, GxB_BITMAP = 4, GxB_FULL = 8 };
 
 typedef struct GB_Type_opaque *GrB_Type;
 typedef struct GB_UnaryOp_opaque *GrB_UnaryOp;
@@ -280,6 +303,15 @@ GrB_Info GrB_Matrix_eWiseAdd_BinaryOp(GrB_Matrix C, const GrB_Matrix Mask, const
                                       const GrB_Descriptor desc);
 GrB_Info GrB_Vector_assign(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
                            const GrB_Vector u, const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc);
+GrB_Info GrB_Vector_apply(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_UnaryOp op,
+                          const GrB_Vector u, const GrB_Descriptor desc);
+GrB_Info GrB_Vector_extract(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Vector u,
+                            const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc);
+GrB_Info GrB_Matrix_reduce_Monoid(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
+                                  const GrB_Monoid monoid, const GrB_Matrix A, const GrB_Descriptor desc);
+GrB_Info GxB_Global_Option_get_INT32(GxB_Option_Field field, int32_t *value);
+GrB_Info GxB_Matrix_Option_get_INT32(GrB_Matrix A, GxB_Option_Field field, int32_t *value);
+GrB_Info GxB_Vector_Option_get_INT32(GrB_Vector v, GxB_Option_Field field, int32_t *value);
 GrB_Info GrB_Matrix_select_INT64(GrB_Matrix C, const GrB_Matrix Mask, const GrB_BinaryOp accum,
                                  const GrB_IndexUnaryOp op, const GrB_Matrix A, int64_t y,
                                  const GrB_Descriptor desc);
@@ -386,6 +418,8 @@ def emit_header():
     L += [f"extern GrB_Type GrB_{t};" for t, _, _ in TYPES]
     L.append("\n/* ---- built-in binary ops (accum / dup / eWise) ---- */")
     L += [f"extern GrB_BinaryOp {n};" for n, *_ in all_binops()]
+    L.append("\n/* ---- built-in unary ops (apply) ---- */")
+    L += [f"extern GrB_UnaryOp {n};" for n, *_ in all_unops()]
     L.append("\n/* ---- index-unary ops for select (tril/triu build the triangle-count input) ---- */")
     L += [f"extern GrB_IndexUnaryOp GrB_{n};" for n in ("TRIL", "TRIU", "DIAG", "OFFDIAG")]
     L.append("\n/* ---- built-in monoids ---- */")
@@ -405,6 +439,9 @@ def emit_lists():
     L.append("")
     L.append("#define GRB_BINOP_LIST(X) \\")
     L += [f"    X({n}, {op}, {x}, {z}) \\" for n, op, x, z in all_binops()]
+    L.append("")
+    L.append("#define GRB_UNOP_LIST(X) \\")
+    L += [f"    X({n}, {op}, {t}) \\" for n, op, t in all_unops()]
     L.append("")
     L.append("#define GRB_MONOID_LIST(X) \\")
     L += [f"    X({n}, {m}, {t}) \\" for n, m, t in all_monoids()]
