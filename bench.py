@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--breakdown", action="store_true", help="print per-kernel device times of the timed region to stderr")
     ap.add_argument("--hub-mode", type=int, default=None, help="libgrb_b200 option hub_mode (0 off, 1 auto, 2 always)")
+    ap.add_argument("--panel-kb", type=int, default=-1, help="column-panel threshold in KB (library option panel_kb; 0 = never)")
     ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
     ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
@@ -65,12 +66,19 @@ def measured_peaks():
 # ---------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.index, self.proc, self.path = index, None, None
+        self.t0 = self.t1 = None
+
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def __enter__(self):
         try:
@@ -95,6 +103,21 @@ class ClockSampler:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         try:
             rows = [ln.split(",") for ln in open(self.path).read().strip().splitlines() if ln.strip()]
+            rows = [r for r in rows if len(r) >= 9]
+            out["window"] = "timed region"
+            if self.t0 is not None and self.t1 is not None:
+                # nvidia-smi is started before the warm-up (its start-up can outlast a short timed region);
+                # keep the samples stamped inside the timed region
+                import datetime
+
+                def stamp(r):
+                    return datetime.datetime.strptime(r[0].strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+
+                inside = [r for r in rows if self.t0 - 0.05 <= stamp(r) <= self.t1 + 0.05]
+                if inside:
+                    rows = inside
+                else:
+                    out["window"] = "warm-up + timed region (the timed region is shorter than one nvidia-smi period)"
             sm = [float(r[1]) for r in rows]
             out["samples"] = len(sm)
             if sm:
@@ -438,6 +461,7 @@ def measure_cpu_baseline(gb, job, r_dev):
 
 
 def run_b200(args):
+    os.environ.setdefault("NCCL_ALGO", "Ring")      # all-gather of 17 MB blocks: 110 us vs 126 us (N = 4) with the default choice
     import torch
     import torch.distributed as dist
 
@@ -456,6 +480,8 @@ def run_b200(args):
         gb.set_option("red_flags", args.red_flags)
     if args.smem_kb:
         gb.set_option("smem_kb", args.smem_kb)
+    if args.panel_kb >= 0:
+        gb.set_option("panel_kb", args.panel_kb)
     scale = args.scale + int(np.log2(world))
     job = PageRankJob(gb, scale, rank, world)
     nnz = job.nnz_total
@@ -465,22 +491,24 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        job.reset()
-        job.step()
-    barrier()
-    # ---- timed region: K steps, device events, kernel timing on ----
-    gb.lib.GxB_b200_kernel_time_reset()
-    gb.set_option("timing", 1)
-    launches0 = gb.launch_count()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank) as clk:         # started before the warm-up: samples are filtered by time stamp
+        for _ in range(max(args.warmup, 3)):
+            job.reset()
+            job.step()
         barrier()
+        # ---- timed region: K steps, device events, kernel timing on ----
+        gb.lib.GxB_b200_kernel_time_reset()
+        gb.set_option("timing", 1)
+        launches0 = gb.launch_count()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        clk.mark_begin()
         ev0.record()
         for _ in range(args.steps):
             job.step()
         ev1.record()
         barrier()
+        clk.mark_end()
     ms = ev0.elapsed_time(ev1)
     gb.set_option("timing", 0)
     launches = gb.launch_count() - launches0

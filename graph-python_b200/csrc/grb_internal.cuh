@@ -77,6 +77,13 @@ struct Csr {
     int64_t n_stiles = 0;
     void *cast_vals = nullptr;     // the values in another type (semiring type != matrix type), kept across calls
     int cast_code = -1;
+    // column panels (csr_ensure_panels): the same rows restricted to column ranges of `panel_width`, so that the
+    // slice of the vector one pull gathers from stays L2-resident when the whole vector does not (multi-GPU row
+    // blocks see all n columns).  Each panel is a full Csr with its own values (in type panel_code) and hub cache.
+    Csr *panels = nullptr;
+    int n_panels = 0;
+    int panel_code = -1;
+    int64_t panel_width = 0;
 };
 
 struct GB_Object {
@@ -140,6 +147,8 @@ struct GrbGlobal {
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
     int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
     int64_t burble = 0;
+    int64_t panel_kb = 24576;      // pull: split a matrix into column panels when the gathered vector exceeds this many KB
+                                   // (0 = never); 24 MB keeps one panel's slice of the vector well inside the 126 MB L2
     int64_t push_edge_ratio = 4;   // push only while (edges leaving the frontier) * ratio <= nnz; beyond that the pull reads less
     int64_t smem_kb = 194;         // shared-memory budget of the hub-table kernels: <= 195 KB keeps the 196 KB carve-out, i.e. 60 KB of L1
                                    // for gather misses in flight (228 KB carve-out: 28 KB L1, gathers 1.5x slower, tools/microbench/gather_bench5)
@@ -198,6 +207,7 @@ void mat_ensure_csc(GB_Object *o);                        // build + cache the t
 void csr_transpose(const Csr &a, Csr &t, size_t tsize);
 void csr_ensure_tiles(Csr &c, int tile_nnz);
 void csr_ensure_hubs(Csr &c, int capacity);               // build / rebuild the hub cache for at most `capacity` hubs
+void csr_ensure_panels(Csr &c, int npanels, const void *vals, int tcode);   // split by column ranges (values in tcode)
 void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)
 const void *csr_vals_as(Csr &c, int from_code, int to_code);   // c.vals, or a cached typed copy of them
 void mat_set_csr(GB_Object *o, Csr &c);                   // take ownership of c as o's CSR

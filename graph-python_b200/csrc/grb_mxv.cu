@@ -204,20 +204,36 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     // (the atomic-segment form also takes a sparse u: Bellman-Ford's `w(min) << w.vxm(A, min_plus)` before w fills up)
     const bool red_shape = !have_mask && !f.comp && (accum < 0 || accum == mon);
     bool use_stream = !pull_any && (a.up == nullptr || red_shape) && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
+    // column panels for the atomic-segment form: when the vector is too large to stay in L2 (a multi-GPU row block
+    // sees all n columns), the rows are split by column ranges and pulled panel by panel into the same output
+    int npanels = 1;
+    if (use_stream && red_shape && g.panel_kb > 0 && M->nnz >= (1 << 20)) {
+        const int64_t bytes = M->ncols * (int64_t)sizeof(T) * (a.up ? 2 : 1);
+        npanels = (int)std::min<int64_t>(8, cdiv(bytes, g.panel_kb * 1024));
+        npanels = (int)std::max<int64_t>(1, std::min<int64_t>(npanels, M->nnz >> 24));    // >= 16 M entries per panel: each
+                                                                                          // panel costs a hub gather + a launch
+    }
     if (use_stream) {
         M->pull_uses++;
-        if (g.hub_mode == 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20))) csr_ensure_hubs(*M, hub_capacity<T>());
-        use_stream = M->hub_col != nullptr && M->hub_n <= hub_capacity<T>();
+        const bool build = g.hub_mode == 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20));
+        if (npanels > 1) {
+            if (build) {
+                csr_ensure_panels(*M, npanels, uses_x ? (const void *)a.av : nullptr, tcode);
+                for (int p = 0; p < M->n_panels; p++) csr_ensure_hubs(M->panels[p], hub_capacity<T>());
+            }
+            use_stream = M->n_panels == npanels && M->panel_code == (uses_x ? tcode : 100 + tcode);
+            for (int p = 0; use_stream && p < M->n_panels; p++)
+                use_stream = M->panels[p].nnz == 0 || (M->panels[p].hub_col != nullptr && M->panels[p].hub_n <= hub_capacity<T>());
+        } else {
+            if (build) csr_ensure_hubs(*M, hub_capacity<T>());
+            use_stream = M->hub_col != nullptr && M->hub_n <= hub_capacity<T>();
+        }
     }
     // ---- atomic-segment pull: no mask, and the write-back is the monoid itself (or a plain overwrite) ----
     if (use_stream && red_shape) {
         const bool pingpong = fused && ((w == u) || (u_vals == w->vals));
         RedArgs<T> ra;
-        ra.pcol = M->hub_col; ra.av = a.av; ra.a_iso = M->iso; ra.u = (const T *)u_vals; ra.up = a.up;
-        ra.hub_n = M->hub_n; ra.nzrow = M->nzrow; ra.chunk_first = M->chunk_first; ra.nnz = M->nnz; ra.ntiles = M->n_stiles;
-        T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
-        GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, ra.up, M->hub_ids, ra.hub_n, hv, hp);
-        ra.hub_v = hv; ra.hub_p = hp; ra.flags = (int)g.red_flags;
+        ra.u = (const T *)u_vals; ra.up = a.up; ra.flags = (int)g.red_flags;
         ra.upairs = nullptr;
         if (ra.up) {      // sparse u: interleave (value, presence) so that one gather fetches both
             pair_bits_t<T> *pairs = (pair_bits_t<T> *)dmalloc((size_t)n_in * sizeof(pair_bits_t<T>));
@@ -240,12 +256,24 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         if (overwrite || !w_full)
             GRB_LAUNCH("red_prefill", k_red_prefill<T>, ew_grid(n_out), 256, 0, ra.w, ra.wp, n_out, ident, (int)overwrite);
         if (!overwrite && w_full) ra.wp = nullptr;     // stays full: no presence traffic at all
-        const bool ok = spmv_launch_red(mon, mul, tcode, &ra);
-        dfree(hv); dfree(hp); dfree((void *)ra.upairs);
+        bool ok = true;
+        const int nparts = npanels > 1 ? M->n_panels : 1;
+        for (int p = 0; ok && p < nparts; p++) {
+            Csr *Mp = npanels > 1 ? &M->panels[p] : M;
+            if (Mp->nnz == 0) continue;
+            ra.pcol = Mp->hub_col; ra.av = npanels > 1 ? (const T *)Mp->vals : a.av; ra.a_iso = Mp->iso;
+            ra.hub_n = Mp->hub_n; ra.nzrow = Mp->nzrow; ra.chunk_first = Mp->chunk_first; ra.nnz = Mp->nnz; ra.ntiles = Mp->n_stiles;
+            T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
+            GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, ra.up, Mp->hub_ids, ra.hub_n, hv, hp);
+            ra.hub_v = hv; ra.hub_p = hp;
+            ok = spmv_launch_red(mon, mul, tcode, &ra);
+            dfree(hv); dfree(hp);
+        }
+        dfree((void *)ra.upairs);
         if (!ok) { dfree(t); dfree(tp); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
         if (fused) {
             if (pingpong) swap_pingpong(w);
-            if (overwrite && !ra.up) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
+            if (overwrite && !ra.up && npanels == 1) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
             else if (!overwrite && w_full) { w->list_valid = false; }
             else { count_present(w->present, n_out, w->d_nvals); vec_set_unknown_nvals(w); }
         } else {

@@ -171,6 +171,8 @@ void csr_drop_caches(Csr &c) {
     dfree(c.nzrow); dfree(c.tile_first); dfree(c.chunk_first); c.nzrow = nullptr; c.tile_first = nullptr; c.chunk_first = nullptr;
     c.n_nzrow = 0; c.n_stiles = 0;
     dfree(c.cast_vals); c.cast_vals = nullptr; c.cast_code = -1;
+    for (int p = 0; p < c.n_panels; p++) csr_free(c.panels[p]);
+    delete[] c.panels; c.panels = nullptr; c.n_panels = 0; c.panel_code = -1; c.panel_width = 0;
 }
 // Matrices are replaced, never edited in place (mat_set_csr), so a typed copy of the values stays valid for the
 // life of the Csr: BOOL adjacency x INT32 vector products cast once, not per call.
@@ -188,6 +190,81 @@ void csr_free(Csr &c) {
     csr_drop_caches(c);
     dfree(c.rowptr); dfree(c.colidx); dfree(c.vals);
     c = Csr();
+}
+
+// ---------------------------------------------------------------- column panels
+constexpr int MAX_PANELS = 8;
+struct PanelPtrs { int64_t *rowptr[MAX_PANELS]; uint32_t *col[MAX_PANELS]; unsigned char *val[MAX_PANELS]; };
+__device__ __forceinline__ int64_t panel_lower_bound(const uint32_t *col, int64_t lo, int64_t hi, uint32_t key) {
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (col[mid] < key) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+// one thread per row: where each panel starts inside the row (absolute entry position) and how many entries it holds
+__global__ void k_panel_split(const int64_t *rowptr, const uint32_t *col, int64_t nrows, int P, int64_t width,
+                              int64_t *start /*[P][nrows]*/, int64_t *count /*[P][nrows+1]*/) {
+    const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (r >= nrows) return;
+    const int64_t e = rowptr[r + 1];
+    int64_t b = rowptr[r];
+    for (int p = 0; p < P; p++) {
+        const int64_t nb = (p + 1 == P) ? e : panel_lower_bound(col, b, e, (uint32_t)((p + 1) * width));
+        start[p * nrows + r] = b;
+        count[p * (nrows + 1) + r] = nb - b;
+        b = nb;
+    }
+}
+__global__ void k_panel_fill(const uint32_t *rows, const uint32_t *col, const unsigned char *vals, int tsize, int iso, int64_t nnz,
+                             int64_t nrows, int64_t width, const int64_t *start, PanelPtrs out) {
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < nnz; e += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t r = rows[e], c = col[e];
+        const int p = (int)(c / width);
+        const int64_t d = out.rowptr[p][r] + (e - start[p * nrows + r]);
+        out.col[p][d] = c;
+        if (!iso) {
+            if (tsize == 4) ((uint32_t *)out.val[p])[d] = ((const uint32_t *)vals)[e];
+            else if (tsize == 8) ((unsigned long long *)out.val[p])[d] = ((const unsigned long long *)vals)[e];
+            else if (tsize == 2) ((uint16_t *)out.val[p])[d] = ((const uint16_t *)vals)[e];
+            else out.val[p][d] = vals[e];
+        }
+    }
+}
+void csr_ensure_panels(Csr &c, int npanels, const void *vals, int tcode) {
+    // vals == nullptr: the multiply ignores the matrix values (second, pair): pattern-only panels, code 100 + tcode
+    if (npanels > MAX_PANELS) npanels = MAX_PANELS;
+    const int code = vals ? tcode : 100 + tcode;
+    if (c.n_panels == npanels && c.panel_code == code) return;
+    for (int p = 0; p < c.n_panels; p++) csr_free(c.panels[p]);
+    delete[] c.panels; c.panels = nullptr; c.n_panels = 0;
+    const int64_t nrows = c.nrows;
+    const int tsize = (int)kTypeSize[tcode];
+    const int64_t width = ((cdiv(c.ncols, npanels) + 1023) / 1024) * 1024;
+    int64_t *start = dalloc<int64_t>((int64_t)npanels * nrows), *count = dalloc<int64_t>((int64_t)npanels * (nrows + 1));
+    dzero(count, (size_t)npanels * (nrows + 1) * sizeof(int64_t));
+    GRB_LAUNCH("panel_split", k_panel_split, nblk(nrows), 256, 0, c.rowptr, c.colidx, nrows, npanels, width, start, count);
+    c.panels = new Csr[npanels];
+    PanelPtrs pp{};
+    size_t tb = 0;
+    CUDA_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tb, count, count, nrows + 1, g.stream));
+    void *tmp = dmalloc(tb);
+    for (int p = 0; p < npanels; p++) {
+        Csr &q = c.panels[p];
+        q.nrows = nrows; q.ncols = c.ncols; q.iso = c.iso || vals == nullptr;
+        q.rowptr = dalloc<int64_t>(nrows + 1);
+        CUDA_TRY(cub::DeviceScan::ExclusiveSum(tmp, tb, count + (int64_t)p * (nrows + 1), q.rowptr, nrows + 1, g.stream));
+        g.launches++;
+        q.nnz = read_i64(q.rowptr + nrows);
+        q.colidx = dalloc<uint32_t>(q.nnz);
+        q.vals = dmalloc(q.iso ? (size_t)tsize : (size_t)(q.nnz > 0 ? q.nnz : 1) * tsize);
+        if (q.iso) { if (vals) d2d(q.vals, vals, (size_t)tsize); else dzero(q.vals, (size_t)tsize); }
+        pp.rowptr[p] = q.rowptr; pp.col[p] = q.colidx; pp.val[p] = (unsigned char *)q.vals;
+    }
+    dfree(tmp);
+    uint32_t *rows = csr_row_ids(c);
+    if (c.nnz)
+        GRB_LAUNCH("panel_fill", k_panel_fill, 148 * 16, 256, 0, rows, c.colidx, (const unsigned char *)vals, tsize, (int)(c.iso || vals == nullptr), c.nnz,
+                   nrows, width, start, pp);
+    dfree(rows); dfree(start); dfree(count);
+    c.n_panels = npanels; c.panel_code = code; c.panel_width = width;
 }
 
 // ---------------------------------------------------------------- hub cache of the pull kernel

@@ -382,3 +382,45 @@ def test_red_pull_sparse_vector(gb, mon, mul, dt, vm, density):
     finally:
         gb.set_option("hub_mode", 1)
         gb.set_option("force_direction", 0)
+
+
+@pytest.mark.parametrize("mon,mul,dt,mdt,vm,density", [("PLUS", "TIMES", "FP32", "FP32", 2, 1.0), ("MIN", "PLUS", "INT64", "INT64", 1, 0.4),
+                                                       ("MIN", "SECOND", "UINT32", "BOOL", 0, 1.0), ("PLUS", "TIMES", "INT64", "INT32", 1, 1.0)])
+@pytest.mark.parametrize("panel_kb", [64, 200])
+def test_red_pull_column_panels(gb, mon, mul, dt, mdt, vm, density, panel_kb):
+    """Column panels (option panel_kb): the pull matrix is split by column ranges so that one panel's slice of the
+    vector stays in L2; every panel accumulates into the same output with the monoid's atomic.  Results must not
+    depend on the split (8 and 3 panels here), with matrix values in the semiring's type, in another type (cast
+    once per matrix) or ignored by the multiply (pattern-only panels)."""
+    from graphblas_b200 import binary
+
+    scale = 17
+    n = 1 << scale
+    A = O.rmat_matrix(scale, mdt, value_mode=vm)
+    gA = gb.Matrix.rmat(scale, mdt, value_mode=vm)
+    At = A.transpose()
+    rng = np.random.default_rng(panel_kb)
+    tol = FP_TOL if dt.startswith("FP") else None
+    gb.set_option("force_direction", 1)
+    gb.set_option("hub_mode", 2)
+    gb.set_option("panel_kb", panel_kb)
+    try:
+        u = _rand_vec(rng, n, dt, density)
+        if dt.startswith("FP"):
+            u.values[:] = u.values / n
+        gu = to_gpu_vector(gb, u)
+        sr = _sr(gb, mon, mul)
+        Ac, Atc = (A, At) if mdt == dt else (A.astype(dt), At.astype(dt))
+        w = O.Vec.empty(n, dt)
+        O.mxv(w, Ac, u, mon, mul, dt)
+        gw = gA.mxv(gu, sr).new()
+        assert vec_equal(gw, w, tol) and gw.nvals == w.nvals
+        acc = getattr(binary, mon.lower())
+        for _ in range(2):
+            O.mxv(w, Ac, u, mon, mul, dt, accum=mon, tran0=True, At=Atc)
+            gw(acc) << gA.T.mxv(gu, sr)
+            assert vec_equal(gw, w, tol) and gw.nvals == w.nvals
+    finally:
+        gb.set_option("panel_kb", 24576)
+        gb.set_option("hub_mode", 1)
+        gb.set_option("force_direction", 0)
