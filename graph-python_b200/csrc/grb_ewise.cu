@@ -205,6 +205,26 @@ __global__ void __launch_bounds__(256) k_ewise_fused(const X *u, const uint8_t *
     block_count_add(e.count, c);
 }
 
+// every operand full, no mask, no accumulator: w = u op v with 128-bit accesses and no presence traffic
+// (PageRank's `w << r.ewise_mult(d, truediv)` between two products)
+template <class X>
+__global__ void __launch_bounds__(256) k_ewise_full(const X *u, const X *v, int op, X *w, int64_t n) {
+    constexpr int VEC = 16 / sizeof(X);
+    const int64_t nvec = n / VEC;
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 a = reinterpret_cast<const uint4 *>(u)[q], b = reinterpret_cast<const uint4 *>(v)[q];
+        X x[VEC], y[VEC], z[VEC];
+        memcpy(x, &a, 16); memcpy(y, &b, 16);
+#pragma unroll
+        for (int k = 0; k < VEC; k++) z[k] = binop_rt<X>(op, x[k], y[k]);
+        uint4 o;
+        memcpy(&o, z, 16);
+        reinterpret_cast<uint4 *>(w)[q] = o;
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = nvec * VEC + threadIdx.x; i < n; i += blockDim.x) w[i] = binop_rt<X>(op, u[i], v[i]);
+}
+
 static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_BinaryOp op,
                          const GrB_Vector u_, const GrB_Vector v_, const GrB_Descriptor desc, bool is_union) {
     require_init();
@@ -225,6 +245,17 @@ static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_Binary
     if (w->type->code == zcode) {
         // both operands full and no mask: the result is full, nvals needs no counting
         const bool known_full = !mask && !f.comp && u->nvals_known && v->nvals_known && u->nvals == n && v->nvals == n;
+        if (known_full && acc < 0 && !cmp && n > 0) {
+            const bool w_was_full = w->nvals_known && w->nvals == n;
+            GRB_TYPE_SWITCH(xcode, X, {
+                GRB_LAUNCH(is_union ? "ewise_add" : "ewise_mult", k_ewise_full<X>, ew_grid(cdiv(n, 16 / (int)sizeof(X))), 256, 0,
+                           (const X *)uv, (const X *)vv, op->op, (X *)w->vals, n);
+            });
+            if (!w_was_full) CUDA_TRY(cudaMemsetAsync(w->present, 1, (size_t)n, g.stream));
+            w->nvals = n; w->nvals_known = true; w->list_valid = false;
+            dfree(uc); dfree(vc);
+            return;
+        }
         if (!known_full) dzero(w->d_nvals, sizeof(int64_t));
         GRB_TYPE_SWITCH(xcode, X, {
             if (cmp) {
