@@ -622,7 +622,11 @@ def run_extra(gb, args):
     ms, (f, st) = timed(lambda: W.cc_min_label(A), reps=2)
     extra[f"cc_min_second_scale{scale}"] = {"ms": ms, "iterations": st["iterations"], "nnz": A.nvals,
                                             "gteps_iters_x_nnz": st["iterations"] * A.nvals / ms / 1e6}
-    del A, f
+    ms, (f2, st) = timed(lambda: W.fastsv(A), reps=2)
+    same = bool(f.isequal(f2))
+    extra[f"fastsv_scale{scale}"] = {"ms": ms, "iterations": st["iterations"], "nnz": A.nvals, "same_labels_as_min_label_cc": same,
+                                     "gteps_iters_x_nnz": st["iterations"] * A.nvals / ms / 1e6}
+    del A, f, f2
     # config 3: triangle counting, masked mxm plus_pair
     for scale in (18, 20):
         A = Matrix.rmat(scale, "INT64", symmetrize=True)
