@@ -145,7 +145,8 @@ struct GrbGlobal {
     // tunables (GxB_b200_set_option)
     int64_t push_ratio = 24;       // push when nvals(u) * push_ratio < n
     int64_t force_direction = 0;   // 0 auto, 1 pull, 2 push
-    int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always
+    int64_t hub_mode = 1;          // 0 never, 1 after the second pull of a matrix with >= 2^20 entries, 2 always,
+                                   // 3 always + scan-based k_spmv_stream for masked / foreign-accumulator write-backs
     int64_t burble = 0;
     int64_t panel_kb = 24576;      // pull: split a matrix into column panels when the gathered vector exceeds this many KB
                                    // (0 = never); 24 MB keeps one panel's slice of the vector well inside the 126 MB L2

@@ -203,11 +203,12 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     // building its stream form (hub ranks, row-start flags) pays off
     // (the atomic-segment form also takes a sparse u: Bellman-Ford's `w(min) << w.vxm(A, min_plus)` before w fills up)
     const bool red_shape = !have_mask && !f.comp && (accum < 0 || accum == mon);
-    bool use_stream = !pull_any && (a.up == nullptr || red_shape) && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
+    const bool red_any = red_shape || g.hub_mode != 3;      // hub_mode 3: keep k_spmv_stream for non-monoid write-backs (A/B)
+    bool use_stream = !pull_any && (a.up == nullptr || red_any) && g.hub_mode && M->nnz > 0 && M->ncols <= (int64_t)COL_MASK;
     // column panels for the atomic-segment form: when the vector is too large to stay in L2 (a multi-GPU row block
     // sees all n columns), the rows are split by column ranges and pulled panel by panel into the same output
     int npanels = 1;
-    if (use_stream && red_shape && g.panel_kb > 0 && M->nnz >= (1 << 20)) {
+    if (use_stream && red_any && g.panel_kb > 0 && M->nnz >= (1 << 20)) {
         const int64_t bytes = M->ncols * (int64_t)sizeof(T) * (a.up ? 2 : 1);
         npanels = (int)std::min<int64_t>(8, cdiv(bytes, g.panel_kb * 1024));
         npanels = (int)std::max<int64_t>(1, std::min<int64_t>(npanels, M->nnz >> 24));    // >= 16 M entries per panel: each
@@ -215,7 +216,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     }
     if (use_stream) {
         M->pull_uses++;
-        const bool build = g.hub_mode == 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20));
+        const bool build = g.hub_mode >= 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20));
         if (npanels > 1) {
             if (build) {
                 csr_ensure_panels(*M, npanels, uses_x ? (const void *)a.av : nullptr, tcode);
@@ -229,9 +230,13 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
             use_stream = M->hub_col != nullptr && M->hub_n <= hub_capacity<T>();
         }
     }
-    // ---- atomic-segment pull: no mask, and the write-back is the monoid itself (or a plain overwrite) ----
-    if (use_stream && red_shape) {
-        const bool pingpong = fused && ((w == u) || (u_vals == w->vals));
+    // ---- atomic-segment pull.  When the write-back is the monoid itself (or a plain overwrite) and there is no mask,
+    // partial sums go straight into w; any other write-back (mask, replace, foreign accumulator, type cast) first
+    // reduces into a temporary t and then runs the dense C-API write-back over it: 190 + 20 us against 380-450 us
+    // for the scan-based k_spmv_stream + fix-up passes on the PageRank graph (tools/debug/masked_variants.py).
+    if (use_stream && (red_shape || g.hub_mode != 3)) {
+        const bool direct = fused && red_shape;
+        const bool pingpong = direct && ((w == u) || (u_vals == w->vals));
         RedArgs<T> ra;
         ra.u = (const T *)u_vals; ra.up = a.up; ra.flags = (int)g.red_flags;
         ra.upairs = nullptr;
@@ -241,9 +246,9 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
             ra.upairs = pairs;
         }
         const T ident = monoid_identity<T>(mon);
-        const bool overwrite = !fused || accum < 0;
-        const bool w_full = fused && w->nvals_known && w->nvals == n_out;
-        if (fused) {
+        const bool overwrite = !direct || accum < 0;
+        const bool w_full = direct && w->nvals_known && w->nvals == n_out;
+        if (direct) {
             if (pingpong) {
                 vec_ensure_alt(w);
                 if (!overwrite) { d2d(w->vals_alt, w->vals, (size_t)n_out * sizeof(T)); d2d(w->present_alt, w->present, (size_t)n_out); }
@@ -271,7 +276,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         }
         dfree((void *)ra.upairs);
         if (!ok) { dfree(t); dfree(tp); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
-        if (fused) {
+        if (direct) {
             if (pingpong) swap_pingpong(w);
             if (overwrite && !ra.up && npanels == 1) { w->nvals = M->n_nzrow; w->nvals_known = true; w->list_valid = false; }
             else if (!overwrite && w_full) { w->list_valid = false; }

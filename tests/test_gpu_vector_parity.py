@@ -210,7 +210,7 @@ def _skewed_matrix(rng, n, dt):
 @pytest.mark.parametrize("mon,mul,dt", [("PLUS", "TIMES", "FP32"), ("PLUS", "TIMES", "INT64"), ("MIN", "PLUS", "INT64"),
                                         ("MIN", "SECOND", "UINT32"), ("PLUS", "PAIR", "INT64"), ("LOR", "LAND", "BOOL"),
                                         ("MAX", "PLUS", "FP64"), ("PLUS", "SECOND", "FP32")])
-@pytest.mark.parametrize("hub_mode", [0, 2])
+@pytest.mark.parametrize("hub_mode", [0, 2, 3])
 def test_stream_pull_full_vector(gb, mon, mul, dt, hub_mode):
     """u full -> k_spmv_stream (hub_mode 2 builds the stream form at once) vs the staged kernel (hub_mode 0) vs oracle;
     masks, accumulators and replace through the fused epilogue; hub rows crossing tiles; empty rows."""
@@ -300,7 +300,8 @@ def test_stream_pull_tile_edges(gb):
 
 @pytest.mark.parametrize("mon,mul,dt,vm", [("PLUS", "TIMES", "INT64", 1), ("PLUS", "TIMES", "FP32", 2), ("MIN", "PLUS", "INT64", 1),
                                            ("MIN", "SECOND", "UINT32", 1)])
-def test_stream_pull_hubs_and_non_hubs(gb, mon, mul, dt, vm):
+@pytest.mark.parametrize("hub_mode", [2, 3])
+def test_stream_pull_hubs_and_non_hubs(gb, mon, mul, dt, vm, hub_mode):
     """A graph with more columns than the shared-memory hub table holds (scale 17: 131072 columns), so both the hub
     and the global-gather lanes of k_spmv_red / k_spmv_stream run; three chained products like the PageRank loop."""
     from graphblas_b200 import binary
@@ -313,7 +314,7 @@ def test_stream_pull_hubs_and_non_hubs(gb, mon, mul, dt, vm):
     rng = np.random.default_rng(33)
     tol = FP_TOL if dt.startswith("FP") else None
     gb.set_option("force_direction", 1)
-    gb.set_option("hub_mode", 2)
+    gb.set_option("hub_mode", hub_mode)
     try:
         u = _rand_vec(rng, n, dt, 1.0)
         if dt.startswith("FP"):
