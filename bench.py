@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--panel-kb", type=int, default=-1, help="column-panel threshold in KB (library option panel_kb; 0 = never)")
     ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
     ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
+    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp"],
+                    help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
+                         "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
     return ap.parse_args()
 
@@ -574,6 +577,168 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------- configs[2]: sharded SSSP
+class SsspJob:
+    """Bellman-Ford `w(min) << w.vxm(A, min_plus)` INT64 (reference notebooks/Intro to GraphBLAS + SSSP example.ipynb
+    cell 21) with the output rows sharded over the ranks: every rank pulls its block
+    `wb(min) << P.mxv(w, min_plus)`, P = its rows of A', then values and presence bytes of the blocks are all-gathered
+    into every rank's full-length w.  The fixed point is detected as in the notebook (w unchanged), by a one-word
+    all-reduce of the per-rank `isequal` results."""
+
+    def __init__(self, gb, scale, rank, world):
+        import torch
+        from graphblas_b200 import Matrix, Vector
+        from graphblas_b200.sharding import BlockExchange
+
+        self.gb, self.rank, self.world, self.n = gb, rank, world, 1 << scale
+        n = self.n
+        A = Matrix.rmat(scale, "INT64", symmetrize=True, value_mode=1)     # same graph on every rank
+        self.nnz_total = A.nvals
+        rp = gb.ffi.new("void**")
+        gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
+        rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+        self.source = int(torch.argmax(rowptr[1:] - rowptr[:-1]).item())
+        self.ex = BlockExchange(n, rank, world)
+        self.lo, self.hi = self.ex.lo, self.ex.hi
+        if world == 1:
+            self.P, self.A = None, A
+        else:
+            AT = A.T.new()
+            self.P = AT.rowblock(self.lo, self.hi)
+            del AT, A
+            self.flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.nnz_local = (self.P if world > 1 else self.A).nvals
+        self.iterations = 0
+        gb.sync()
+
+    def _tensors(self, v, n):
+        gb = self.gb
+        vals, pres = gb.ffi.new("void**"), gb.ffi.new("void**")
+        assert gb.lib.GxB_b200_Vector_device_ptrs(vals, pres, v._carg) == gb.lib.GrB_SUCCESS
+        return (dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), n, "<i8"),
+                dev_tensor(int(gb.ffi.cast("uintptr_t", pres[0])), n, "|u1"))
+
+    def step(self):
+        import torch.distributed as dist
+        from graphblas_b200 import Vector, binary, semiring
+
+        gb, n, nb = self.gb, self.n, self.hi - self.lo
+        if self.world == 1:
+            from graphblas_b200 import workloads as W
+
+            self.w, st = W.sssp_bellman_ford(self.A, self.source)
+            self.iterations = st["iterations"]
+            return
+        w = Vector("INT64", n)
+        w[self.source] = 0
+        wb = Vector("INT64", nb)
+        if self.lo <= self.source < self.hi:
+            wb[self.source - self.lo] = 0
+        iters = 0
+        while True:
+            prev = wb.dup()
+            wb(binary.min) << self.P.mxv(w, semiring.min_plus)
+            iters += 1
+            same = bool(wb.isequal(prev))
+            self.flag.fill_(0 if same else 1)
+            dist.all_reduce(self.flag, op=dist.ReduceOp.MAX)
+            if int(self.flag.item()) == 0:
+                break
+            wv, wp = self._tensors(w, n)
+            bv, bp = self._tensors(wb, nb)
+            self.ex.all_gather(wv, bv)
+            self.ex.all_gather(wp, bp)
+            gb.lib.GxB_b200_Vector_set_dense_nvals(w._carg, -1)
+        self.w, self.wb, self.iterations = w, wb, iters
+
+
+def run_sssp(args):
+    """`bench.py --workload sssp [--gpus N] [--scale 24]`: BASELINE configs[2]; one step = one run to the fixed point."""
+    os.environ.setdefault("NCCL_ALGO", "Ring")
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: libgrb_b200 has no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import graphblas_b200 as gb
+
+    gb.init("b200")
+    gb.use_torch_stream()
+    job = SsspJob(gb, args.scale, rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    steps = args.steps
+    with ClockSampler(local_rank) as clk:
+        for _ in range(max(args.warmup, 3)):
+            job.step()
+        barrier()
+        gb.lib.GxB_b200_kernel_time_reset()
+        gb.set_option("timing", 1)
+        clk.mark_begin()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = gb.launch_count()
+        ev0.record()
+        for _ in range(steps):
+            job.step()
+        ev1.record()
+        barrier()
+        clk.mark_end()
+        ms = ev0.elapsed_time(ev1)
+        launches = gb.launch_count() - l0
+    gb.set_option("timing", 0)
+    if args.breakdown and rank == 0:
+        gb.lib.GxB_b200_kernel_time_dump()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # parity across shardings: a checksum of the distances (sum and count of reached vertices), identical for every N
+    if world == 1:
+        vals, pres = job.w.to_dense()
+        reached, checksum = int(pres.sum()), int(vals[pres.astype(bool)].sum())
+    else:
+        bv, bp = job._tensors(job.wb, job.hi - job.lo)
+        part = torch.stack([bp.to(torch.int64).sum(), (bv * bp.to(torch.int64)).sum()])
+        dist.all_reduce(part)
+        reached, checksum = int(part[0].item()), int(part[1].item())
+    nnz, iters = job.nnz_total, job.iterations
+    k_ms, k_cnt = kernel_time(gb, "spmv_red")
+    k2_ms, k2_cnt = kernel_time(gb, "spmv_red_sparse")
+    if k2_ms > k_ms:
+        k_ms, k_cnt = k2_ms, k2_cnt
+    peak, peak_src = measured_peaks()
+    alg = job.nnz_local * (4 + 8 + 8) + (job.hi - job.lo) * (8 + 8 + 8)
+    line = {"metric": METRIC, "value": steps * iters * nnz / ms / 1e6, "unit": "GTEPS", "n_gpus": world, "steps": steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "config": {"workload": f"Bellman-Ford SSSP to the fixed point: w(min) << w.vxm(A, min_plus) INT64, symmetrised R-MAT scale "
+                                   f"{args.scale} edgefactor 16 (BASELINE configs[2]), output rows sharded over {world} GPU(s), "
+                                   "all-gather of values + presence per iteration; TEPS = iterations x nnz / time",
+                       "scale": args.scale, "nnz": nnz, "iterations": iters, "parallelism": f"{world} GPU(s), 1-D row blocks",
+                       "reached": reached, "distance_checksum": checksum,
+                       "l2": "inputs larger than L2; no explicit flush"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_red<min_plus,int64> (dominant pull kernel)",
+                         "achieved": (alg / (k_ms / k_cnt) / 1e6) if k_cnt else None, "peak": peak, "unit": "GB/s",
+                         "frac": (alg / (k_ms / k_cnt) / 1e6 / peak) if k_cnt else None, "traffic": None,
+                         "algorithmic_bytes_per_launch": int(alg), "avg_launch_ms": (k_ms / k_cnt) if k_cnt else None,
+                         "launches_timed": k_cnt, "kernel_share_of_step": (k_ms / ms) if ms else None,
+                         "peak_source": peak_src},
+            "clocks": clk.summary()}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_extra(gb, args):
     """The other BASELINE configs on one GPU (extra keys of the JSON line; not the headline metric)."""
     import torch
@@ -583,6 +748,7 @@ def run_extra(gb, args):
         fn()                                   # warm-up (builds cached transposes / stream forms)
         best, out = None, None
         for _ in range(reps):
+            out = None                         # release the previous result first (SpGEMM scale 20: 116 GB of output)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -628,14 +794,14 @@ def run_extra(gb, args):
                                      "gteps_iters_x_nnz": st["iterations"] * A.nvals / ms / 1e6}
     del A, f, f2
     # config 3: triangle counting, masked mxm plus_pair
-    for scale in (18, 20):
+    for scale in (20, 22):
         A = Matrix.rmat(scale, "INT64", symmetrize=True)
         ms, (ntri, st) = timed(lambda: W.triangle_count(A), reps=2)
         extra[f"tc_plus_pair_scale{scale}"] = {"ms": ms, "triangles": ntri, "nnz_L": st["nnz_L"], "mask_nnz_per_s": st["nnz_L"] / ms * 1e3,
                                                "triangles_per_s": ntri / ms * 1e3}
         del A
     # config 4a: SpGEMM A.mxm(A) plus_times FP64
-    for scale in (16, 18):
+    for scale in (18, 20):
         A = Matrix.rmat(scale, "FP64", value_mode=2)
         ms, (C, st) = timed(lambda: W.spgemm(A), reps=2)
         extra[f"spgemm_plus_times_fp64_scale{scale}"] = {"ms": ms, "nnz_A": A.nvals, "nnz_C": st["nnz_C"], "out_nnz_per_s": st["nnz_C"] / ms * 1e3}
@@ -647,6 +813,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "sssp":
+        run_sssp(args)
     else:
         run_b200(args)
 

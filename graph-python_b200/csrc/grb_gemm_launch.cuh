@@ -4,7 +4,7 @@
 #pragma once
 #include "grb_internal.cuh"
 
-enum GemmKernel { GK_WARP = 0, GK_BLOCK = 1, GK_DENSE = 2 };
+enum GemmKernel { GK_WARP = 0, GK_BLOCK = 1, GK_DENSE = 2, GK_PANEL = 3 };
 struct GemmLaunch {
     int kernel;          // GemmKernel
     int grid, threads;

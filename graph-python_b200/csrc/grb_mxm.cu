@@ -140,6 +140,12 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
     const int64_t words = cdiv(n, 32);
     const size_t bm_bytes = (size_t)words * 4;
     const bool bm_in_smem = bm_bytes <= 200 * 1024;
+    // heavy rows: shared-memory column panels (k_panel_symbolic / k_panel_row) when the row bitmap fits shared memory
+    const int np = (int)cdiv(n > 0 ? n : 1, PANEL_W);
+    const bool panels = g.spgemm_panels && bm_in_smem && np <= PANEL_MAX_NP;
+    uint16_t *rowS = panels ? dalloc<uint16_t>(m) : nullptr;
+    unsigned long long *cursor = (unsigned long long *)(g.d_scratch + 48);
+    uint32_t *ptab = nullptr;
     // ---- symbolic ----
     {
         Bins bins;
@@ -149,11 +155,17 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
         a.Bp = B.rowptr; a.Bj = B.colidx; a.Bx = nullptr; a.b_iso = 1;
         a.nrows = m; a.ncols = n; a.rownnz = rownnz; a.Cp = nullptr; a.Cj = nullptr; a.Cx = nullptr;
         a.gbitmap = nullptr; a.gacc = nullptr; a.words = words;
+        a.ptab = nullptr; a.np = np; a.rowS = rowS; a.cursor = cursor;
         for (int b = 1; b < NBINS; b++) {
             const int64_t nb = bins.off[b + 1] - bins.off[b];
             if (!nb) continue;
             a.rows = bins.rows + bins.off[b]; a.nbin = nb;
-            if (b == 1) {
+            if (b == NBINS - 1 && panels) {
+                auto kern = k_panel_symbolic;
+                if (bm_bytes > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm_bytes));
+                dzero(cursor, sizeof(unsigned long long));
+                GRB_LAUNCH("spgemm_symbolic_panel", kern, (int)(nb < g.sm_count ? nb : g.sm_count), PANEL_THREADS, bm_bytes, a);
+            } else if (b == 1) {
                 auto kern = k_hash_warp<SymSR, false>;
                 GRB_LAUNCH("spgemm_symbolic_warp", kern, (int)cdiv(nb, HW_ROWS), HW_ROWS * 32, 0, a);
             } else if (b < NBINS - 1) {
@@ -192,6 +204,7 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
         a.Bp = B.rowptr; a.Bj = B.colidx; a.Bx = (const T *)B.vals; a.b_iso = B.iso;
         a.nrows = m; a.ncols = n; a.rownnz = nullptr; a.Cp = Tout.rowptr; a.Cj = Tout.colidx; a.Cx = (T *)Tout.vals;
         a.gbitmap = nullptr; a.gacc = nullptr; a.words = words;
+        a.ptab = nullptr; a.np = np; a.rowS = rowS; a.cursor = cursor;
         for (int b = 1; b < NBINS; b++) {
             const int64_t nb = bins.off[b + 1] - bins.off[b];
             if (!nb) continue;
@@ -199,8 +212,18 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
             GemmLaunch L;
             L.args = &a; L.table = kBinTable[b]; L.threads = kBinThreads[b]; L.smem = 0;
             uint32_t *gb = nullptr; T *gacc = nullptr;
-            if (b == 1) { L.kernel = GK_WARP; L.grid = (int)cdiv(nb, HW_ROWS); }
-            else if (b < NBINS - 1) { L.kernel = GK_BLOCK; L.grid = (int)nb; L.smem = (size_t)kBinTable[b] * (4 + sizeof(T)); }
+            if (b == NBINS - 1 && panels) {
+                if (np > 1) {
+                    ptab = dalloc<uint32_t>(B.nrows * (int64_t)(np + 1));
+                    GRB_LAUNCH("spgemm_panel_table", k_panel_table, nblk(B.nrows * 32), 256, 0, B.rowptr, B.colidx, B.nrows, np, ptab);
+                    a.ptab = ptab;
+                }
+                dzero(cursor, sizeof(unsigned long long));
+                L.kernel = GK_PANEL; L.grid = (int)(nb < g.sm_count ? nb : g.sm_count); L.threads = PANEL_THREADS;
+                L.smem = panel_row_smem<T>();
+                if (g.spgemm_panels == 2) { gacc = dalloc<T>((int64_t)L.grid * PANEL_TABLE); a.gacc = gacc; }
+            } else if (b == 1) { L.kernel = GK_WARP; L.grid = (int)cdiv(nb, HW_ROWS); }
+            else if (b < NBINS - 1) { L.kernel = GK_BLOCK; L.grid = (int)nb; L.smem = hash_block_smem(kBinTable[b], sizeof(T)); }
             else {
                 L.kernel = GK_DENSE;
                 int64_t grid = nb < 2 * g.sm_count ? nb : 2 * g.sm_count;
@@ -214,12 +237,12 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
                 a.gbitmap = gb; a.gacc = gacc;
             }
             const bool ok = gemm_launch_numeric(mon, mul, tcode, L);
-            dfree(gb); dfree(gacc);
-            a.gbitmap = nullptr; a.gacc = nullptr;
-            if (!ok) { dfree(ub); dfree(counts); csr_free(Tout); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
+            dfree(gb); dfree(gacc); dfree(ptab); ptab = nullptr;
+            a.gbitmap = nullptr; a.gacc = nullptr; a.ptab = nullptr;
+            if (!ok) { dfree(ub); dfree(counts); dfree(rowS); csr_free(Tout); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
         }
     }
-    dfree(ub); dfree(counts);
+    dfree(ub); dfree(counts); dfree(rowS);
 }
 
 // ---------------------------------------------------------------- masked dot: T<M> = A (+).(x) B with B given as rows of B'

@@ -4,8 +4,16 @@
 // of their products ub = min(flops(i), ncols):
 //   k_hash_warp    ub <= 32     one warp per row, 64-slot shared-memory hash table
 //   k_hash_block   ub <= 8192   one CTA per row, 1K / 8K / 16K-slot shared-memory hash table (up to 192 KB)
-//   k_dense_block  ub  > 8192   hub rows: presence bitmap in shared memory (ncols bits) + a dense accumulator
-//                               row per CTA in HBM (L2-resident); ordered extraction by popcount prefix sums
+//   k_panel_symbolic / k_panel_row   ub > 8192, the rows that hold > 95 % of the products of an R-MAT A*A:
+//                               symbolic = whole-row presence bitmap in shared memory (ncols bits), which also
+//                               yields the entries per 16 K-column base panel; numeric = the row's columns are cut
+//                               into ranges of s base panels (s the largest power of two whose ranges each hold
+//                               <= 10 240 entries), one 16 K-slot shared-memory hash table per range, or a dense
+//                               16 K-entry accumulator + bitmap when a single base panel overflows the table.
+//                               B rows are cut at panel boundaries through a per-row offset table (ptab), so a
+//                               range only reads its own slice of B.  Accumulators never leave shared memory.
+//   k_dense_block  fallback of the above when ncols bits do not fit shared memory: per-CTA bitmap + dense
+//                               accumulator row in HBM; ordered extraction by popcount prefix sums
 // Hash rows are sorted in shared memory (bitonic) before they are written, so every output row is sorted and
 // output patterns are bit-exact against the oracle.  Algorithmic bytes:
 //   nnz(A)*(4+V) + flops*(4+V) + nnz(C)*(4+V) + 2*n*8  (+ flops*4 + n*8 for the symbolic pass).
@@ -32,6 +40,11 @@ template <class T> struct GemmArgs {
     uint32_t *gbitmap;       // per-CTA bitmaps in HBM when ncols bits do not fit shared memory (else nullptr)
     T *gacc;                 // per-CTA dense accumulator rows, pre-filled with the monoid identity
     int64_t words;           // bitmap words = ceil(ncols / 32)
+    // panel path (k_panel_symbolic / k_panel_row)
+    const uint32_t *ptab;    // [B rows][np + 1]: offset inside B row k of the first entry with column >= q * PANEL_W
+    int np;                  // base panels = ceil(ncols / PANEL_W)
+    uint16_t *rowS;          // per row: base panels per hash range (power of two), 0 = dense accumulator per base panel
+    unsigned long long *cursor;   // dynamic row scheduler
 };
 
 template <class T> __device__ __forceinline__ T ld_val(const T *p, int iso, int64_t k) { return p[iso ? 0 : k]; }
@@ -70,6 +83,144 @@ __device__ __forceinline__ void bitonic_sort(uint32_t *keys, T *vals, int n, int
             }
             if (WARP) __syncwarp(); else __syncthreads();
         }
+    }
+}
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *s_warp /* >= 33 ints */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < nwarps ? s_warp[lane] : 0;
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+        s_warp[lane] = w;          // inclusive warp totals
+    }
+    __syncthreads();
+    const int base = warp ? s_warp[warp - 1] : 0;
+    *total = s_warp[nwarps - 1];
+    __syncthreads();
+    return base + x - v;
+}
+
+
+// Emit a shared-memory hash table in key order without sorting the table: keys are dealt into nbk order-preserving
+// buckets ((key - min) >> shift, about 8 entries each), a counting pass places slot numbers bucket by bucket, one
+// thread orders each bucket by insertion, and the row leaves through coalesced stores.  O(table) work against the
+// O(table log^2 table) of a bitonic sort (measured: 140 us -> a few us per 16 K-slot table).  A bucket with more
+// than HASH_BUCKET_MAX entries (clustered keys) falls back to the bitonic sort.  Returns the entry count.
+//   slot: >= (entries) uint16;  bpos: >= nbk uint32;  s_tmp: >= 40 ints;  nbk a power of two
+constexpr int HASH_BUCKET_MAX = 48;
+template <class T> __device__ __forceinline__ T ld_acc(const T *p, bool global_vals) { return global_vals ? *(const volatile T *)p : *p; }
+template <class T, bool GV = false>
+__device__ __forceinline__ int hash_emit_sorted(uint32_t *keys, T *vals, int table, uint16_t *slot, uint32_t *bpos, int nbk,
+                                                uint32_t *Cj, T *Cx, int64_t out, int *s_tmp) {
+    const int tid = threadIdx.x, nthreads = blockDim.x, lane = tid & 31;
+    uint32_t *s_min = (uint32_t *)&s_tmp[33], *s_max = (uint32_t *)&s_tmp[34];
+    int *s_flag = &s_tmp[35];
+    for (int b = tid; b < nbk; b += nthreads) bpos[b] = 0;
+    if (tid == 0) { *s_min = 0xFFFFFFFFu; *s_max = 0; *s_flag = 0; }
+    __syncthreads();
+    uint32_t lo = 0xFFFFFFFFu, hi = 0;
+    for (int k = tid; k < table; k += nthreads) { const uint32_t key = keys[k]; if (key != HASH_EMPTY) { lo = min(lo, key); hi = max(hi, key); } }
+    for (int o = 16; o; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+    if (lane == 0 && lo != 0xFFFFFFFFu) { atomicMin(s_min, lo); atomicMax(s_max, hi); }
+    __syncthreads();
+    lo = *s_min; hi = *s_max;
+    if (lo == 0xFFFFFFFFu) return 0;
+    int sh = 0;
+    while (((hi - lo) >> sh) >= (uint32_t)nbk) sh++;
+    for (int k = tid; k < table; k += nthreads) { const uint32_t key = keys[k]; if (key != HASH_EMPTY) atomicAdd(&bpos[(key - lo) >> sh], 1u); }
+    __syncthreads();
+    // exclusive scan of the bucket counts (each thread owns `per` consecutive buckets)
+    const int per = (nbk + nthreads - 1) / nthreads;
+    int c = 0;
+    for (int b = tid * per; b < min(nbk, (tid + 1) * per); b++) c += (int)bpos[b];
+    int total;
+    int off = block_exclusive_scan(c, &total, s_tmp);
+    for (int b = tid * per; b < min(nbk, (tid + 1) * per); b++) { const int n = (int)bpos[b]; bpos[b] = (uint32_t)off; off += n; }
+    __syncthreads();
+    for (int k = tid; k < table; k += nthreads) {
+        const uint32_t key = keys[k];
+        if (key != HASH_EMPTY) slot[atomicAdd(&bpos[(key - lo) >> sh], 1u)] = (uint16_t)k;
+    }
+    __syncthreads();
+    // bpos[b] is now the end of bucket b
+    for (int b = tid; b < nbk; b += nthreads) {
+        const int beg = b ? (int)bpos[b - 1] : 0, end = (int)bpos[b];
+        if (end - beg > HASH_BUCKET_MAX) { *s_flag = 1; continue; }
+        for (int i = beg + 1; i < end; i++) {
+            const uint16_t si = slot[i];
+            const uint32_t ki = keys[si];
+            int j = i - 1;
+            while (j >= beg && keys[slot[j]] > ki) { slot[j + 1] = slot[j]; j--; }
+            slot[j + 1] = si;
+        }
+    }
+    __syncthreads();
+    if (*s_flag) {
+        bitonic_sort<T, false>(keys, vals, table, tid, nthreads);
+        for (int k = tid; k < total; k += nthreads) { Cj[out + k] = keys[k]; Cx[out + k] = ld_acc(&vals[k], GV); }
+    } else {
+        for (int k = tid; k < total; k += nthreads) { const int sl = slot[k]; Cj[out + k] = keys[sl]; Cx[out + k] = ld_acc(&vals[sl], GV); }
+    }
+    return total;
+}
+
+// Every product of one row of A with the slice [q0, q1) (base panels) of the B rows it selects: f(pA, qB).
+// A CTA takes blockDim.x entries of the A row at a time, one per thread, so the dependent loads Aj -> Bp -> ptab of a
+// whole batch are in flight together.  B segments of <= 16 entries are walked by their lane, up to 64 by the warp,
+// longer ones go to a shared-memory queue that all warps of the CTA drain in 32-entry chunks dealt round-robin: a hub
+// row of B met by one lane must not keep the other 31 warps waiting at the barrier that ends the range (ncu: 91 % of
+// the stall samples of the first version sat on that barrier).
+// (Flattening the 32 segments of a warp with a scan + shuffle search was measured 1.4-4x SLOWER on R-MAT: the search
+// costs more than the idle lanes it saves.)
+constexpr int PANEL_SHORT = 16;       // a lane walks a B segment of up to this many entries alone
+constexpr int PANEL_LONG = 64;        // longer segments are shared by the whole CTA
+constexpr int SEGQ_CAP = 256;
+struct SegQueue { long long s0[SEGQ_CAP]; int len[SEGQ_CAP]; int poff[SEGQ_CAP]; int n; };
+template <class F>
+__device__ __forceinline__ void panel_products(const int64_t *Ap, const uint32_t *Aj, const int64_t *Bp, int64_t row,
+                                               const uint32_t *ptab, int np, int q0, int q1, SegQueue *sq, F &&f) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int64_t pb = Ap[row], pe = Ap[row + 1];
+    for (int64_t base = pb; base < pe; base += blockDim.x) {
+        if (tid == 0) sq->n = 0;
+        __syncthreads();
+        const int64_t p = base + tid;
+        int64_t s0 = 0; int len = 0;
+        if (p < pe) {
+            const uint32_t k = Aj[p];
+            const int64_t bs = Bp[k];
+            if (ptab) { const uint32_t *t = ptab + (int64_t)k * (np + 1); const uint32_t o0 = t[q0]; s0 = bs + o0; len = (int)(t[q1] - o0); }
+            else { s0 = bs; len = (int)(Bp[k + 1] - bs); }
+        }
+        if (len > PANEL_LONG) {
+            const int e = atomicAdd(&sq->n, 1);
+            if (e < SEGQ_CAP) { sq->s0[e] = s0; sq->len[e] = len; sq->poff[e] = (int)(p - pb); len = 0; }   // else: the warp keeps it
+        }
+        if (len <= PANEL_SHORT) for (int q = 0; q < len; q++) f(p, s0 + q);
+        unsigned m = __ballot_sync(0xffffffffu, len > PANEL_SHORT);
+        while (m) {
+            const int l = __ffs(m) - 1; m &= m - 1;
+            const int64_t ws = __shfl_sync(0xffffffffu, s0, l), wp = __shfl_sync(0xffffffffu, p, l);
+            const int wl = __shfl_sync(0xffffffffu, len, l);
+            for (int q = lane; q < wl; q += 32) f(wp, ws + q);
+        }
+        __syncthreads();
+        const int nq = sq->n < SEGQ_CAP ? sq->n : SEGQ_CAP;
+        int cum = 0;
+        for (int e = 0; e < nq; e++) {
+            const int L = sq->len[e], nch = (L + 31) >> 5;
+            const int64_t es = sq->s0[e], ep = pb + sq->poff[e];
+            for (int c = (warp - cum % nwarps + nwarps) % nwarps; c < nch; c += nwarps) {
+                const int q = c * 32 + lane;
+                if (q < L) f(ep, es + q);
+            }
+            cum += nch;
+        }
+        __syncthreads();
     }
 }
 
@@ -120,6 +271,7 @@ __global__ void k_hash_block(GemmArgs<typename SR::type> a, int table) {
     uint32_t *keys = (uint32_t *)smem_raw;
     T *vals = (T *)(smem_raw + (size_t)table * sizeof(uint32_t));
     __shared__ int s_cnt;
+    __shared__ int s_tmp[40];
     const int tid = threadIdx.x, nthreads = blockDim.x;
     const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
     const int64_t row = a.rows[blockIdx.x];
@@ -143,32 +295,16 @@ __global__ void k_hash_block(GemmArgs<typename SR::type> a, int table) {
         __syncthreads();
         if (tid == 0) a.rownnz[row] = s_cnt;
     } else {
-        bitonic_sort<T, false>(keys, vals, table, tid, nthreads);
-        const int64_t o = a.Cp[row];
-        const int cnt = (int)(a.Cp[row + 1] - o);
-        for (int k = tid; k < cnt; k += nthreads) { a.Cj[o + k] = keys[k]; a.Cx[o + k] = vals[k]; }
+        // numeric rows are binned by their exact size: at most table / 2 entries
+        uint16_t *slot = (uint16_t *)(smem_raw + (size_t)table * (sizeof(uint32_t) + sizeof(T)));
+        uint32_t *bpos = (uint32_t *)(smem_raw + (size_t)table * (sizeof(uint32_t) + sizeof(T) + 1));
+        hash_emit_sorted<T>(keys, vals, table, slot, bpos, table / 8, a.Cj, a.Cx, a.Cp[row], s_tmp);
     }
 }
+// dynamic shared memory of k_hash_block<SR, true>: table, slot list (table / 2 x uint16), bucket cursors (table / 8 x uint32)
+inline size_t hash_block_smem(int table, size_t tsize) { return (size_t)table * (4 + tsize + 1) + (size_t)(table / 8) * 4; }
 
-// ---- hub rows: bitmap + dense accumulator, CTAs loop over the bin ----
-__device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *s_warp /* >= 33 ints */) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    int x = v;
-    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-    if (lane == 31) s_warp[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-        int w = lane < nwarps ? s_warp[lane] : 0;
-        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
-        s_warp[lane] = w;          // inclusive warp totals
-    }
-    __syncthreads();
-    const int base = warp ? s_warp[warp - 1] : 0;
-    *total = s_warp[nwarps - 1];
-    __syncthreads();
-    return base + x - v;
-}
-
+// ---- hub rows (fallback): bitmap + dense accumulator in HBM, CTAs loop over the bin ----
 template <class SR, bool NUMERIC>
 __global__ void k_dense_block(GemmArgs<typename SR::type> a) {
     using T = typename SR::type;
@@ -223,6 +359,167 @@ __global__ void k_dense_block(GemmArgs<typename SR::type> a) {
         }
         __threadfence_block();
         __syncthreads();
+    }
+}
+
+// ---- heavy rows: column panels, accumulators in shared memory ----
+constexpr int PANEL_W = 16384;        // columns per base panel = entries of the dense accumulator
+constexpr int PANEL_TABLE = 16384;    // hash slots per range
+constexpr int PANEL_CAP = 10240;      // entries a range may hold (load factor 0.625)
+constexpr int PANEL_THREADS = 1024;
+constexpr int PANEL_MAX_NP = 256;     // base panels (ncols <= 4 Mi); beyond that the HBM dense path runs
+
+// ptab[k][q] for one B row per warp
+static __global__ void __launch_bounds__(256) k_panel_table(const int64_t *Bp, const uint32_t *Bj, int64_t brows, int np, uint32_t *ptab) {
+    const int64_t k = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (k >= brows) return;
+    const int64_t bs = Bp[k], be = Bp[k + 1];
+    for (int q = lane; q <= np; q += 32) {
+        const uint64_t key = (uint64_t)q * PANEL_W;
+        int64_t lo = bs, hi = be;
+        if (q == 0) hi = lo;
+        while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if ((uint64_t)Bj[mid] < key) lo = mid + 1; else hi = mid; }
+        ptab[k * (np + 1) + q] = (uint32_t)(lo - bs);
+    }
+}
+
+__device__ __forceinline__ int warp_max(int v) { for (int o = 16; o; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o)); return v; }
+
+// symbolic pass of the heavy rows: entries per row, and how the numeric pass will cut the row (rowS)
+static __global__ void __launch_bounds__(PANEL_THREADS, 1) k_panel_symbolic(GemmArgs<int32_t> a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *bm = (uint32_t *)smem_raw;
+    __shared__ int s_pc[PANEL_MAX_NP];
+    __shared__ SegQueue s_q;
+    __shared__ long long s_r;
+    const int tid = threadIdx.x, nthreads = blockDim.x, lane = tid & 31;
+    for (int64_t w = tid; w < a.words; w += nthreads) bm[w] = 0;
+    const int64_t chunk = (a.words + nthreads - 1) / nthreads;
+    while (true) {
+        if (tid == 0) s_r = (long long)atomicAdd(a.cursor, 1ull);
+        if (tid < PANEL_MAX_NP) s_pc[tid] = 0;
+        __syncthreads();
+        const int64_t r = s_r;
+        if (r >= a.nbin) break;
+        const int64_t row = a.rows[r];
+        const uint32_t *Bj = a.Bj;
+        panel_products(a.Ap, a.Aj, a.Bp, row, nullptr, 1, 0, 1, &s_q, [&](int64_t, int64_t q) {
+            const uint32_t j = Bj[q];
+            const uint32_t bit = 1u << (j & 31);
+            if (!(bm[j >> 5] & bit)) atomicOr(&bm[j >> 5], bit);
+        });
+        __syncthreads();
+        // entries per base panel (PANEL_W / 32 = 512 words each); the bitmap is cleared on the way
+        const int64_t w0 = tid * chunk, w1 = (w0 + chunk < a.words) ? w0 + chunk : a.words;
+        int c = 0; int64_t cur = w0 >> 9;
+        for (int64_t w = w0; w < w1; w++) {
+            if ((w >> 9) != cur) { if (c) atomicAdd(&s_pc[cur], c); c = 0; cur = w >> 9; }
+            c += __popc(bm[w]);
+            bm[w] = 0;
+        }
+        if (c) atomicAdd(&s_pc[cur], c);
+        __syncthreads();
+        if (tid < 32) {
+            // lane owns base panels 8*lane .. 8*lane+7; m[g] = the fullest range when ranges are 2^g base panels wide
+            int cnt[8];
+            for (int i = 0; i < 8; i++) cnt[i] = s_pc[lane * 8 + i];
+            int m[9];
+            m[0] = 0; for (int i = 0; i < 8; i++) m[0] = max(m[0], cnt[i]);
+            m[1] = 0; for (int i = 0; i < 8; i += 2) m[1] = max(m[1], cnt[i] + cnt[i + 1]);
+            m[2] = max(cnt[0] + cnt[1] + cnt[2] + cnt[3], cnt[4] + cnt[5] + cnt[6] + cnt[7]);
+            int f = cnt[0] + cnt[1] + cnt[2] + cnt[3] + cnt[4] + cnt[5] + cnt[6] + cnt[7];
+            m[3] = f;
+            for (int g = 4; g < 9; g++) { f += __shfl_xor_sync(0xffffffffu, f, 1 << (g - 4)); m[g] = f; }
+            const int total = m[8];
+            int best = -1;
+            for (int g = 8; g >= 0; g--) { const int mx = warp_max(m[g]); if (best < 0 && mx <= PANEL_CAP) best = g; }
+            // ranges of one base panel always take the dense accumulator (it holds any count and needs no hashing)
+            if (lane == 0) { a.rownnz[row] = total; a.rowS[row] = best < 1 ? (uint16_t)1 : (uint16_t)(1u << best); }
+        }
+        __syncthreads();
+    }
+}
+
+// numeric pass of the heavy rows
+// dynamic shared memory: hash view = 16 K keys + 16 K values + slot list (PANEL_CAP x uint16) + 2 K bucket cursors;
+//                        dense view = 16 K values + 16 K presence bits
+template <class T> constexpr size_t panel_row_smem() {
+    constexpr size_t hash_b = (size_t)PANEL_TABLE * (4 + sizeof(T)) + (size_t)PANEL_CAP * 2 + (PANEL_TABLE / 8) * 4;
+    constexpr size_t dense_b = (size_t)PANEL_W * sizeof(T) + PANEL_W / 8;
+    return hash_b > dense_b ? hash_b : dense_b;
+}
+// GV: the values live in a per-CTA 16 K-entry buffer in global memory (a.gacc; 148 x 128 KB stays in L2) and are combined
+// with L2 atomics (RED), keys / presence bits stay in shared memory.  Shared-memory atomics on 8-byte floating-point
+// values are compare-and-swap loops; the L2 path is fire-and-forget.
+template <class SR, bool GV>
+__global__ void __launch_bounds__(PANEL_THREADS, 1) k_panel_row(GemmArgs<typename SR::type> a) {
+    using T = typename SR::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    // hash view
+    uint32_t *keys = (uint32_t *)smem_raw;
+    T *vals = GV ? a.gacc + (size_t)blockIdx.x * PANEL_TABLE : (T *)(smem_raw + (size_t)PANEL_TABLE * sizeof(uint32_t));
+    uint16_t *slot = (uint16_t *)(smem_raw + (size_t)PANEL_TABLE * (sizeof(uint32_t) + sizeof(T)));
+    uint32_t *bpos = (uint32_t *)(smem_raw + (size_t)PANEL_TABLE * (sizeof(uint32_t) + sizeof(T)) + (size_t)PANEL_CAP * 2);
+    // dense view
+    T *acc = GV ? a.gacc + (size_t)blockIdx.x * PANEL_TABLE : (T *)smem_raw;
+    uint32_t *bm = (uint32_t *)(smem_raw + (size_t)PANEL_W * sizeof(T));
+    __shared__ int s_tmp[40];
+    __shared__ long long s_r;
+    __shared__ SegQueue s_q;
+    const int tid = threadIdx.x;
+    while (true) {
+        if (tid == 0) s_r = (long long)atomicAdd(a.cursor, 1ull);
+        __syncthreads();
+        const int64_t r = s_r;
+        if (r >= a.nbin) break;
+        const int64_t row = a.rows[r];
+        const int s = a.rowS[row];
+        const bool dense = (s == 1);
+        int64_t out = a.Cp[row];
+        for (int q0 = 0; q0 < a.np; q0 += s) {
+            const int q1 = (q0 + s < a.np) ? q0 + s : a.np;
+            const uint32_t c0 = (uint32_t)q0 * PANEL_W;
+            const uint32_t *ptab = (q0 == 0 && q1 == a.np) ? nullptr : a.ptab;   // a range over every panel reads whole B rows
+            int total;
+            if (dense) {
+                for (int k = tid; k < PANEL_W; k += PANEL_THREADS) acc[k] = SR::Mon::identity();
+                if (tid < PANEL_W / 32) bm[tid] = 0;
+                __syncthreads();
+                panel_products(a.Ap, a.Aj, a.Bp, row, ptab, a.np, q0, q1, &s_q, [&](int64_t p, int64_t q) {
+                    const uint32_t j = a.Bj[q] - c0;
+                    const uint32_t bit = 1u << (j & 31);
+                    if (!(bm[j >> 5] & bit)) atomicOr(&bm[j >> 5], bit);
+                    const T av = SR::kUsesX ? ld_val(a.Ax, a.a_iso, p) : (T)0;
+                    const T bv = SR::kUsesY ? ld_val(a.Bx, a.b_iso, q) : (T)0;
+                    SR::Mon::atomic(&acc[j], SR::mult(av, bv));
+                });
+                if (GV) __threadfence();
+                __syncthreads();
+                // ordered extraction: thread t owns columns 16 t .. 16 t + 15 of the panel
+                uint32_t bits = (bm[tid >> 1] >> ((tid & 1) * 16)) & 0xffffu;
+                int64_t o = out + block_exclusive_scan(__popc(bits), &total, s_tmp);
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    a.Cj[o] = c0 + tid * 16 + b; a.Cx[o] = ld_acc(&acc[tid * 16 + b], GV);
+                    o++;
+                }
+            } else {
+                for (int k = tid; k < PANEL_TABLE; k += PANEL_THREADS) { keys[k] = HASH_EMPTY; vals[k] = SR::Mon::identity(); }
+                __syncthreads();
+                panel_products(a.Ap, a.Aj, a.Bp, row, ptab, a.np, q0, q1, &s_q, [&](int64_t p, int64_t q) {
+                    const T av = SR::kUsesX ? ld_val(a.Ax, a.a_iso, p) : (T)0;
+                    const T bv = SR::kUsesY ? ld_val(a.Bx, a.b_iso, q) : (T)0;
+                    hash_insert<SR, true>(keys, vals, PANEL_TABLE - 1, a.Bj[q], SR::mult(av, bv));
+                });
+                if (GV) __threadfence();
+                __syncthreads();
+                total = hash_emit_sorted<T, GV>(keys, vals, PANEL_TABLE, slot, bpos, PANEL_TABLE / 8, a.Cj, a.Cx, out, s_tmp);
+            }
+            out += total;
+            __syncthreads();
+        }
     }
 }
 

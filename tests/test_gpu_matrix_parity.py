@@ -84,6 +84,43 @@ def test_spgemm_hub_rows_dense_path(gb):
     assert mat_equal(gC, T)
 
 
+@pytest.mark.parametrize("panels", [1, 0])
+def test_spgemm_heavy_rows_hash_ranges(gb, panels):
+    """Heavy rows whose columns are cut into several shared-memory hash ranges (7 base panels of 16 K columns,
+    ranges of 2), next to the HBM dense-accumulator fallback (spgemm_panels = 0): same bits either way."""
+    rng = np.random.default_rng(7)
+    n = 100000
+    A = _rand_mat(rng, 48, n, 48 * 300, "FP64")       # 48 rows x ~300 entries
+    B = _rand_mat(rng, n, n, n * 100, "FP64")         # ~30000 products per row of A
+    gA, gB = to_gpu_matrix(gb, A), to_gpu_matrix(gb, B)
+    gb.set_option("spgemm_panels", panels)
+    try:
+        T = O.spgemm(A, B, "PLUS", "TIMES", "FP64")
+        gC = gA.mxm(gB, _sr("PLUS", "TIMES")).new()
+        assert mat_equal(gC, T, FP_TOL), gb.last_kernel()
+        T = O.spgemm(A, B, "MIN", "SECOND", "FP64")
+        gC = gA.mxm(gB, _sr("MIN", "SECOND")).new()
+        assert mat_equal(gC, T), gb.last_kernel()
+    finally:
+        gb.set_option("spgemm_panels", 1)
+
+
+def test_spgemm_rmat_scale14_fp64(gb):
+    """BASELINE config 5a in small: A.mxm(A, plus_times) FP64 on a directed R-MAT graph, where > 80 % of the
+    products sit in heavy rows (hash ranges and dense base panels); pattern exact, values within 1e-5."""
+    A = O.rmat_matrix(14, "FP64", value_mode=2)
+    gA = to_gpu_matrix(gb, A)
+    T = O.spgemm(A, A, "PLUS", "TIMES", "FP64")
+    gC = gA.mxm(gA, _sr("PLUS", "TIMES")).new()
+    assert gC.nvals == T.nnz
+    assert mat_equal(gC, T, FP_TOL), gb.last_kernel()
+    # integer semiring on the same pattern: bit-exact
+    Ai = O.rmat_matrix(14, "INT64", value_mode=1)
+    Ti = O.spgemm(Ai, Ai, "PLUS", "TIMES", "INT64")
+    gCi = to_gpu_matrix(gb, Ai).mxm(to_gpu_matrix(gb, Ai), _sr("PLUS", "TIMES")).new()
+    assert mat_equal(gCi, Ti), gb.last_kernel()
+
+
 def test_spgemm_nonsquare_and_empty(gb):
     rng = np.random.default_rng(6)
     A = _rand_mat(rng, 37, 91, 400, "FP64")
