@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
+    ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
+    ap.add_argument("--spgemm-scale", type=int, default=20)
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
     return ap.parse_args()
 
@@ -562,6 +564,12 @@ def run_b200(args):
         e2e = None if args.no_e2e else measure_e2e_sharded(gb, job, args)      # collective: every rank takes part
         if rank == 0:
             line["e2e"] = e2e
+    if rank == 0 and world == 1 and not args.no_spgemm:
+        del job
+        try:
+            line["spgemm"] = measure_spgemm(gb, args.spgemm_scale)
+        except Exception as exc:                 # the contract line must survive a failure of the second leg
+            line["spgemm"] = {"error": f"{type(exc).__name__}: {exc}"}
     if rank == 0 and world == 1 and args.extra:
         if args.breakdown:
             gb.lib.GxB_b200_kernel_time_reset()
@@ -737,6 +745,57 @@ def run_sssp(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def measure_spgemm(gb, scale, reps=2):
+    """The second half of BASELINE's metric: output entries per second of C = A.mxm(A, plus_times) FP64 on a directed
+    R-MAT graph (configs[4]; scale 20: 16 M entries in, 20.9 G products, 9.7 G entries = 116 GB out).  Device-timed
+    through the public API (`A.mxm(A).new()`), graph resident in HBM, the previous result released first.  Algorithmic
+    bytes: nnz(A)*(I+V) + flops*(I+V) + nnz(C)*(I+V) + 2*n*P for the numeric pass + flops*I + n*P for the
+    symbolic pass, with I = 4, V = 8, P = 8 and no cache credit for the re-read rows of B."""
+    import torch
+    from graphblas_b200 import Matrix, workloads as W
+
+    A = Matrix.rmat(scale, "FP64", value_mode=2)
+    n, nnz_a = A.nrows, A.nvals
+    rp, ci = gb.ffi.new("void**"), gb.ffi.new("void**")
+    gb.lib.GxB_b200_Matrix_device_ptrs(rp, ci, gb.ffi.NULL, A._carg)
+    rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+    colidx = dev_tensor(int(gb.ffi.cast("uintptr_t", ci[0])), nnz_a, "<i4")
+    outdeg = rowptr[1:] - rowptr[:-1]
+    indeg = torch.bincount(colidx.to(torch.int64), minlength=n)
+    flops = int((indeg * outdeg).sum().item())
+    del indeg, outdeg
+    C, st = W.spgemm(A)                        # warm-up
+    nnz_c = st["nnz_C"]
+    del C
+    times = []
+    gb.lib.GxB_b200_kernel_time_reset()
+    gb.set_option("timing", 1)
+    l0 = gb.launch_count()
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        C, st = W.spgemm(A)
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1))
+        del C
+    launches = gb.launch_count() - l0
+    gb.set_option("timing", 0)
+    k_ms, k_cnt = kernel_time(gb, "spgemm_numeric_panel")
+    s_ms, s_cnt = kernel_time(gb, "spgemm_symbolic_panel")
+    ms = sum(times) / len(times)
+    alg = nnz_a * 12 + flops * 12 + nnz_c * 12 + 2 * n * 8 + flops * 4 + n * 8
+    peak, peak_src = measured_peaks()
+    return {"workload": f"C = A.mxm(A, plus_times) FP64, directed R-MAT scale {scale} edgefactor 16 (BASELINE configs[4])",
+            "value": nnz_c / ms * 1e3, "unit": "output entries/s", "ms": ms, "ms_best": min(times), "reps": reps,
+            "nnz_A": nnz_a, "nnz_C": nnz_c, "products": flops, "products_per_s": flops / ms * 1e3, "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": alg / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": alg / ms / 1e6 / peak,
+                         "algorithmic_bytes": int(alg), "peak_source": peak_src,
+                         "numeric_heavy_rows_ms": (k_ms / k_cnt) if k_cnt else None,
+                         "symbolic_heavy_rows_ms": (s_ms / s_cnt) if s_cnt else None}}
 
 
 def run_extra(gb, args):

@@ -239,24 +239,39 @@ static void matrix_ewise(GrB_Matrix C_, const GrB_Matrix M_, const GrB_BinaryOp 
 }
 
 // ---------------------------------------------------------------- select (tril / triu / diag / offdiag)
-template <bool FILL>
-__global__ void __launch_bounds__(128) k_mat_select(const int64_t *Ap, const uint32_t *Aj, int64_t nrows, int op,
-                                                    int64_t y, int64_t *rownnz, const int64_t *Op, int64_t *src) {
+// Rows are sorted by column, so every positional predicate keeps one contiguous run of a row (tril: a prefix, triu: a
+// suffix, diag: at most one entry) or everything but one entry (offdiag): two binary searches per row instead of a
+// walk over its entries (a thread per row walking a 27 K-entry hub row made select 7 of the 42 ms of triangle counting).
+//   first[i] = position of the first kept entry, skip[i] = position of the dropped entry for offdiag (else -1)
+__global__ void __launch_bounds__(256) k_select_ranges(const int64_t *Ap, const uint32_t *Aj, int64_t nrows, int op, int64_t y,
+                                                       int64_t *rownnz, int64_t *first, int64_t *skip) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= nrows) return;
-    int64_t o = FILL ? Op[i] : 0, cnt = 0;
-    for (int64_t p = Ap[i], e = Ap[i + 1]; p < e; p++) {
-        const int64_t d = (int64_t)Aj[p] - i;   // j - i
-        bool keep;
-        switch (op) {
-        case IDX_TRIL: keep = d <= y; break;
-        case IDX_TRIU: keep = d >= y; break;
-        case IDX_DIAG: keep = d == y; break;
-        default: keep = d != y; break;
-        }
-        if (keep) { if (FILL) src[o++] = p; else cnt++; }
+    const int64_t s = Ap[i], e = Ap[i + 1];
+    const int64_t t = i + y;                          // target column: j - i (<=, >=, ==, !=) y
+    // lb = first position with j >= t, ub = first position with j > t
+    int64_t lo = s, hi = e;
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if ((int64_t)Aj[mid] < t) lo = mid + 1; else hi = mid; }
+    const int64_t lb = lo;
+    const int64_t ub = (lb < e && (int64_t)Aj[lb] == t) ? lb + 1 : lb;
+    int64_t f = s, cnt = 0, sk = -1;
+    switch (op) {
+    case IDX_TRIL: f = s; cnt = ub - s; break;
+    case IDX_TRIU: f = lb; cnt = e - lb; break;
+    case IDX_DIAG: f = lb; cnt = ub - lb; break;
+    default: f = s; cnt = (e - s) - (ub - lb); sk = (ub > lb) ? lb : -1; break;
     }
-    if (!FILL) rownnz[i] = cnt;
+    rownnz[i] = cnt; first[i] = f; skip[i] = sk;
+}
+__global__ void __launch_bounds__(256) k_select_src(const uint32_t *rowid, const int64_t *Op, const int64_t *first, const int64_t *skip,
+                                                    int64_t n, int64_t *src) {
+    const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t i = rowid[k];
+    int64_t p = first[i] + (k - Op[i]);
+    const int64_t sk = skip[i];
+    if (sk >= 0 && p >= sk) p++;
+    src[k] = p;
 }
 template <class T>
 __global__ void k_gather_entries(const int64_t *src, int64_t n, const uint32_t *Aj, const T *Ax, int iso, uint32_t *Oj, T *Ox) {
@@ -279,12 +294,16 @@ static void matrix_select(GB_Object *C, GB_Object *mask, int acc, int idxop, GB_
     T.nrows = S.nrows; T.ncols = S.ncols; T.iso = S.iso;
     int64_t *counts = dalloc<int64_t>(n + 1);
     T.rowptr = dalloc<int64_t>(n + 1);
-    GRB_LAUNCH("mat_select_count", k_mat_select<false>, nblk(n, 128), 128, 0, S.rowptr, S.colidx, n, idxop, y, counts,
-               (const int64_t *)nullptr, (int64_t *)nullptr);
+    int64_t *first = dalloc<int64_t>(n + 1), *skip = dalloc<int64_t>(n + 1);
+    GRB_LAUNCH("mat_select_ranges", k_select_ranges, nblk(n, 256), 256, 0, S.rowptr, S.colidx, n, idxop, y, counts, first, skip);
     T.nnz = scan_counts(counts, T.rowptr, n);
     int64_t *src = dalloc<int64_t>(T.nnz);
-    GRB_LAUNCH("mat_select_fill", k_mat_select<true>, nblk(n, 128), 128, 0, S.rowptr, S.colidx, n, idxop, y, counts,
-               (const int64_t *)T.rowptr, src);
+    if (T.nnz) {
+        uint32_t *rowid = csr_row_ids(T);
+        GRB_LAUNCH("mat_select_src", k_select_src, nblk(T.nnz, 256), 256, 0, rowid, (const int64_t *)T.rowptr, first, skip, T.nnz, src);
+        dfree(rowid);
+    }
+    dfree(first); dfree(skip);
     T.colidx = dalloc<uint32_t>(T.nnz);
     const size_t ts = A->type->size;
     T.vals = dmalloc(T.iso ? ts : (size_t)(T.nnz > 0 ? T.nnz : 1) * ts);

@@ -164,7 +164,7 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
                 auto kern = k_panel_symbolic;
                 if (bm_bytes > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bm_bytes));
                 dzero(cursor, sizeof(unsigned long long));
-                GRB_LAUNCH("spgemm_symbolic_panel", kern, (int)(nb < g.sm_count ? nb : g.sm_count), PANEL_THREADS, bm_bytes, a);
+                GRB_LAUNCH("spgemm_symbolic_panel", kern, (int)(nb < g.sm_count ? nb : g.sm_count), PSYM_THREADS, bm_bytes, a);
             } else if (b == 1) {
                 auto kern = k_hash_warp<SymSR, false>;
                 GRB_LAUNCH("spgemm_symbolic_warp", kern, (int)cdiv(nb, HW_ROWS), HW_ROWS * 32, 0, a);
@@ -219,7 +219,7 @@ static void gustavson_typed(const Csr &A, const Csr &B, int mon, int mul, int tc
                     a.ptab = ptab;
                 }
                 dzero(cursor, sizeof(unsigned long long));
-                L.kernel = GK_PANEL; L.grid = (int)(nb < g.sm_count ? nb : g.sm_count); L.threads = PANEL_THREADS;
+                L.kernel = GK_PANEL; L.grid = (int)(nb < PANEL_CTAS_PER_SM * g.sm_count ? nb : PANEL_CTAS_PER_SM * g.sm_count); L.threads = PANEL_THREADS;
                 L.smem = panel_row_smem<T>();
                 if (g.spgemm_panels == 2) { gacc = dalloc<T>((int64_t)L.grid * PANEL_TABLE); a.gacc = gacc; }
             } else if (b == 1) { L.kernel = GK_WARP; L.grid = (int)cdiv(nb, HW_ROWS); }

@@ -86,21 +86,24 @@ def test_spgemm_hub_rows_dense_path(gb):
 
 @pytest.mark.parametrize("panels", [1, 0])
 def test_spgemm_heavy_rows_hash_ranges(gb, panels):
-    """Heavy rows whose columns are cut into several shared-memory hash ranges (7 base panels of 16 K columns,
-    ranges of 2), next to the HBM dense-accumulator fallback (spgemm_panels = 0): same bits either way."""
+    """Heavy rows whose columns are cut into several shared-memory hash ranges or dense base panels (25 base panels
+    of 4 K columns), next to the HBM dense-accumulator fallback (spgemm_panels = 0): same bits either way."""
     rng = np.random.default_rng(7)
     n = 100000
-    A = _rand_mat(rng, 48, n, 48 * 300, "FP64")       # 48 rows x ~300 entries
-    B = _rand_mat(rng, n, n, n * 100, "FP64")         # ~30000 products per row of A
-    gA, gB = to_gpu_matrix(gb, A), to_gpu_matrix(gb, B)
+    B = _rand_mat(rng, n, n, n * 100, "FP64")
+    gB = to_gpu_matrix(gb, B)
     gb.set_option("spgemm_panels", panels)
     try:
-        T = O.spgemm(A, B, "PLUS", "TIMES", "FP64")
-        gC = gA.mxm(gB, _sr("PLUS", "TIMES")).new()
-        assert mat_equal(gC, T, FP_TOL), gb.last_kernel()
-        T = O.spgemm(A, B, "MIN", "SECOND", "FP64")
-        gC = gA.mxm(gB, _sr("MIN", "SECOND")).new()
-        assert mat_equal(gC, T), gb.last_kernel()
+        # ~11 000 products per row (sparse ranges: hash tables over several base panels) and ~30 000 (dense base panels)
+        for per_row in (110, 300):
+            A = _rand_mat(rng, 48, n, 48 * per_row, "FP64")
+            gA = to_gpu_matrix(gb, A)
+            T = O.spgemm(A, B, "PLUS", "TIMES", "FP64")
+            gC = gA.mxm(gB, _sr("PLUS", "TIMES")).new()
+            assert mat_equal(gC, T, FP_TOL), (per_row, gb.last_kernel())
+            T = O.spgemm(A, B, "MIN", "SECOND", "FP64")
+            gC = gA.mxm(gB, _sr("MIN", "SECOND")).new()
+            assert mat_equal(gC, T), (per_row, gb.last_kernel())
     finally:
         gb.set_option("spgemm_panels", 1)
 
