@@ -588,7 +588,6 @@ __device__ __forceinline__ int64_t lower_bound_u32(const uint32_t *col, int64_t 
 }
 
 constexpr int DOT_THREADS = 256;
-constexpr int DOT_ILP = 1;           // binary searches in flight per lane on the warp path (2 and 4 were measured slower: 49 vs 34 ms at scale 20)
 constexpr int DOT_SERIAL_MAX = 32;   // a thread handles the pair alone if the shorter row has <= this many entries
 
 template <class SR>
@@ -641,38 +640,16 @@ __global__ void __launch_bounds__(DOT_THREADS) k_dot_masked(DotArgs<typename SR:
         const uint32_t *sc = a_short ? a.Aj : a.Bj, *lc = a_short ? a.Bj : a.Aj;
         const int64_t ss = a_short ? as : bs, se = a_short ? ae : be, ls = a_short ? bs : as, le = a_short ? be : ae;
         T acc = Mon::identity(); bool has = false;
-        // DOT_ILP binary searches per lane run in lockstep: the search is a chain of dependent L2 loads, and one chain per
-        // lane leaves the memory system idle (the kernel is bound by latency x chains in flight, not by bandwidth)
-        for (int64_t sp0 = ss + lane; sp0 < se; sp0 += 32 * DOT_ILP) {
-            uint32_t key[DOT_ILP]; int64_t lo[DOT_ILP], hi[DOT_ILP];
-#pragma unroll
-            for (int u = 0; u < DOT_ILP; u++) {
-                const int64_t sp = sp0 + 32 * u;
-                const bool on = sp < se;
-                key[u] = on ? sc[sp] : 0u;
-                lo[u] = ls; hi[u] = on ? le : ls;
-            }
-            bool more = true;
-            while (more) {
-                more = false;
-#pragma unroll
-                for (int u = 0; u < DOT_ILP; u++) {
-                    if (lo[u] < hi[u]) {
-                        const int64_t mid = (lo[u] + hi[u]) >> 1;
-                        if (lc[mid] < key[u]) lo[u] = mid + 1; else hi[u] = mid;
-                        more |= lo[u] < hi[u];
-                    }
-                }
-            }
-#pragma unroll
-            for (int u = 0; u < DOT_ILP; u++) {
-                const int64_t sp = sp0 + 32 * u;
-                if (sp < se && lo[u] < le && lc[lo[u]] == key[u]) {
-                    const int64_t pa = a_short ? sp : lo[u], pb = a_short ? lo[u] : sp;
-                    const T z = SR::mult(SR::kUsesX ? ld_val(a.Ax, a.a_iso, pa) : (T)0,
-                                         SR::kUsesY ? ld_val(a.Bx, a.b_iso, pb) : (T)0);
-                    acc = has ? Mon::apply(acc, z) : z; has = true;
-                }
+        // (Running 2-4 of these searches per lane in lockstep was measured SLOWER, 49 vs 34 ms at scale 20: the kernel is
+        // bound by L1 wavefronts of the diverging lower levels of the search, not by the latency of one chain.)
+        for (int64_t sp = ss + lane; sp < se; sp += 32) {
+            const uint32_t key = sc[sp];
+            const int64_t lo = lower_bound_u32(lc, ls, le, key);
+            if (lo < le && lc[lo] == key) {
+                const int64_t pa = a_short ? sp : lo, pb = a_short ? lo : sp;
+                const T z = SR::mult(SR::kUsesX ? ld_val(a.Ax, a.a_iso, pa) : (T)0,
+                                     SR::kUsesY ? ld_val(a.Bx, a.b_iso, pb) : (T)0);
+                acc = has ? Mon::apply(acc, z) : z; has = true;
             }
         }
         for (int off = 16; off; off >>= 1) {
