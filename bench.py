@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--panel-kb", type=int, default=-1, help="column-panel threshold in KB (library option panel_kb; 0 = never)")
     ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
     ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
-    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp"],
+    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
@@ -587,20 +587,31 @@ def run_b200(args):
 
 # ---------------------------------------------------------------------------------------------- configs[2]: sharded SSSP
 class SsspJob:
-    """Bellman-Ford `w(min) << w.vxm(A, min_plus)` INT64 (reference notebooks/Intro to GraphBLAS + SSSP example.ipynb
-    cell 21) with the output rows sharded over the ranks: every rank pulls its block
-    `wb(min) << P.mxv(w, min_plus)`, P = its rows of A', then values and presence bytes of the blocks are all-gathered
-    into every rank's full-length w.  The fixed point is detected as in the notebook (w unchanged), by a one-word
-    all-reduce of the per-rank `isequal` results."""
+    """Fixed-point vector-product loops with the output rows sharded over the ranks.
 
-    def __init__(self, gb, scale, rank, world):
+    kind "sssp": Bellman-Ford `w(min) << w.vxm(A, min_plus)` INT64 (reference notebooks/Intro to GraphBLAS + SSSP
+    example.ipynb cell 21): every rank pulls its block `wb(min) << P.mxv(w, min_plus)`, P = its rows of A', then values
+    and presence bytes of the blocks are all-gathered into every rank's full-length w.
+    kind "cc": FastSV's product `mngp << A.mxv(gp, min_second)` folded into min-label propagation
+    `f(min) << A.mxv(f, min_second)` UINT32 (notebooks/Connected Components -- FastSV.ipynb cells 17, 30); f is full, so
+    only values are exchanged.
+    The fixed point is detected as in the notebooks (vector unchanged), by a one-word all-reduce of the per-rank
+    `isequal` results."""
+
+    def __init__(self, gb, scale, rank, world, kind="sssp"):
         import torch
         from graphblas_b200 import Matrix, Vector
         from graphblas_b200.sharding import BlockExchange
 
-        self.gb, self.rank, self.world, self.n = gb, rank, world, 1 << scale
+        self.gb, self.rank, self.world, self.n, self.kind = gb, rank, world, 1 << scale, kind
         n = self.n
-        A = Matrix.rmat(scale, "INT64", symmetrize=True, value_mode=1)     # same graph on every rank
+        if kind == "sssp":
+            A = Matrix.rmat(scale, "INT64", symmetrize=True, value_mode=1)     # same graph on every rank
+            self.dtype, self.typestr, self.vsize = "INT64", "<i8", 8
+        else:
+            A = Matrix.rmat(scale, "BOOL", symmetrize=True)
+            self.dtype, self.typestr, self.vsize = "UINT32", "<i4", 4     # labels < 2^31: int32 view for torch / NCCL
+        self.msize = 8 if kind == "sssp" else 0        # bytes of A's values the multiply reads (second ignores A)
         self.nnz_total = A.nvals
         rp = gb.ffi.new("void**")
         gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
@@ -611,19 +622,26 @@ class SsspJob:
         if world == 1:
             self.P, self.A = None, A
         else:
-            AT = A.T.new()
-            self.P = AT.rowblock(self.lo, self.hi)
-            del AT, A
+            if kind == "sssp":
+                AT = A.T.new()
+                self.P = AT.rowblock(self.lo, self.hi)
+                del AT
+            else:
+                self.P = A.rowblock(self.lo, self.hi)
+            del A
             self.flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self.nnz_local = (self.P if world > 1 else self.A).nvals
         self.iterations = 0
+        if kind == "cc":                       # initial labels stay on the device; a step starts from copies of them
+            self.f0 = Vector.from_dense(np.arange(n, dtype=np.uint32))
+            self.f0b = Vector.from_dense(np.arange(self.lo, self.hi, dtype=np.uint32))
         gb.sync()
 
     def _tensors(self, v, n):
         gb = self.gb
         vals, pres = gb.ffi.new("void**"), gb.ffi.new("void**")
         assert gb.lib.GxB_b200_Vector_device_ptrs(vals, pres, v._carg) == gb.lib.GrB_SUCCESS
-        return (dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), n, "<i8"),
+        return (dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), n, self.typestr),
                 dev_tensor(int(gb.ffi.cast("uintptr_t", pres[0])), n, "|u1"))
 
     def step(self):
@@ -634,18 +652,23 @@ class SsspJob:
         if self.world == 1:
             from graphblas_b200 import workloads as W
 
-            self.w, st = W.sssp_bellman_ford(self.A, self.source)
+            self.w, st = W.sssp_bellman_ford(self.A, self.source) if self.kind == "sssp" else W.cc_min_label(self.A, f0=self.f0)
             self.iterations = st["iterations"]
             return
-        w = Vector("INT64", n)
-        w[self.source] = 0
-        wb = Vector("INT64", nb)
-        if self.lo <= self.source < self.hi:
-            wb[self.source - self.lo] = 0
+        if self.kind == "sssp":
+            w = Vector("INT64", n)
+            w[self.source] = 0
+            wb = Vector("INT64", nb)
+            if self.lo <= self.source < self.hi:
+                wb[self.source - self.lo] = 0
+            sr = semiring.min_plus
+        else:
+            w, wb = self.f0.dup(), self.f0b.dup()
+            sr = semiring.min_second
         iters = 0
         while True:
             prev = wb.dup()
-            wb(binary.min) << self.P.mxv(w, semiring.min_plus)
+            wb(binary.min) << self.P.mxv(w, sr)
             iters += 1
             same = bool(wb.isequal(prev))
             self.flag.fill_(0 if same else 1)
@@ -655,8 +678,9 @@ class SsspJob:
             wv, wp = self._tensors(w, n)
             bv, bp = self._tensors(wb, nb)
             self.ex.all_gather(wv, bv)
-            self.ex.all_gather(wp, bp)
-            gb.lib.GxB_b200_Vector_set_dense_nvals(w._carg, -1)
+            if self.kind == "sssp":
+                self.ex.all_gather(wp, bp)
+                gb.lib.GxB_b200_Vector_set_dense_nvals(w._carg, -1)
         self.w, self.wb, self.iterations = w, wb, iters
 
 
@@ -675,7 +699,8 @@ def run_sssp(args):
 
     gb.init("b200")
     gb.use_torch_stream()
-    job = SsspJob(gb, args.scale, rank, world)
+    kind = args.workload
+    job = SsspJob(gb, args.scale, rank, world, kind)
 
     def barrier():
         if world > 1:
@@ -713,31 +738,40 @@ def run_sssp(args):
         reached, checksum = int(pres.sum()), int(vals[pres.astype(bool)].sum())
     else:
         bv, bp = job._tensors(job.wb, job.hi - job.lo)
-        part = torch.stack([bp.to(torch.int64).sum(), (bv * bp.to(torch.int64)).sum()])
+        part = torch.stack([bp.to(torch.int64).sum(), (bv.to(torch.int64) * bp.to(torch.int64)).sum()])
         dist.all_reduce(part)
         reached, checksum = int(part[0].item()), int(part[1].item())
     nnz, iters = job.nnz_total, job.iterations
+    # the pull kernel of this loop: full-vector and sparse-vector variants, one launch per column panel of the block
+    # (a product = `panels` launches), so the roofline is taken per PRODUCT: algorithmic bytes of one product / the
+    # device time of its launches
     k_ms, k_cnt = kernel_time(gb, "spmv_red")
     k2_ms, k2_cnt = kernel_time(gb, "spmv_red_sparse")
-    if k2_ms > k_ms:
-        k_ms, k_cnt = k2_ms, k2_cnt
+    k_ms, k_cnt = k_ms + k2_ms, k_cnt + k2_cnt
+    products = steps * iters
+    panels = max(1, round(k_cnt / max(products, 1)))
+    k_ms_per_product = k_ms / max(products, 1)
     peak, peak_src = measured_peaks()
-    alg = job.nnz_local * (4 + 8 + 8) + (job.hi - job.lo) * (8 + 8 + 8)
+    alg = job.nnz_local * (4 + job.msize + job.vsize) + (job.hi - job.lo) * (8 + 2 * job.vsize)
     line = {"metric": METRIC, "value": steps * iters * nnz / ms / 1e6, "unit": "GTEPS", "n_gpus": world, "steps": steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": f"Bellman-Ford SSSP to the fixed point: w(min) << w.vxm(A, min_plus) INT64, symmetrised R-MAT scale "
-                                   f"{args.scale} edgefactor 16 (BASELINE configs[2]), output rows sharded over {world} GPU(s), "
-                                   "all-gather of values + presence per iteration; TEPS = iterations x nnz / time",
+            "vs_baseline": None, "dtype": "int64" if kind == "sssp" else "u32", "data": "synthetic",
+            "config": {"workload": (f"Bellman-Ford SSSP to the fixed point: w(min) << w.vxm(A, min_plus) INT64, symmetrised R-MAT scale "
+                                    f"{args.scale} edgefactor 16 (BASELINE configs[2]), output rows sharded over {world} GPU(s), "
+                                    "all-gather of values + presence per iteration; TEPS = iterations x nnz / time") if kind == "sssp" else
+                                   (f"Connected components by FastSV's product folded into min-label propagation: f(min) << A.mxv(f, min_second) "
+                                    f"UINT32 to the fixed point, symmetrised R-MAT scale {args.scale} edgefactor 16 (BASELINE configs[4]b), output "
+                                    f"rows sharded over {world} GPU(s), all-gather of the labels per iteration; TEPS = iterations x nnz / time"),
                        "scale": args.scale, "nnz": nnz, "iterations": iters, "parallelism": f"{world} GPU(s), 1-D row blocks",
                        "reached": reached, "distance_checksum": checksum,
                        "l2": "inputs larger than L2; no explicit flush"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_spmv_red<min_plus,int64> (dominant pull kernel)",
-                         "achieved": (alg / (k_ms / k_cnt) / 1e6) if k_cnt else None, "peak": peak, "unit": "GB/s",
-                         "frac": (alg / (k_ms / k_cnt) / 1e6 / peak) if k_cnt else None, "traffic": None,
-                         "algorithmic_bytes_per_launch": int(alg), "avg_launch_ms": (k_ms / k_cnt) if k_cnt else None,
-                         "launches_timed": k_cnt, "kernel_share_of_step": (k_ms / ms) if ms else None,
+            "roofline": {"bound": "hbm", "kernel": "k_spmv_red<min_plus,int64> (dominant pull kernel)" if kind == "sssp" else "k_spmv_red<min_second,u32>",
+                         "achieved": (alg / k_ms_per_product / 1e6) if k_cnt else None, "peak": peak, "unit": "GB/s",
+                         "frac": (alg / k_ms_per_product / 1e6 / peak) if k_cnt else None, "traffic": None,
+                         "algorithmic_bytes_per_product": int(alg), "ms_per_product": k_ms_per_product if k_cnt else None,
+                         "launches_per_product": panels, "launches_timed": k_cnt,
+                         "kernel_share_of_step": (k_ms / ms) if ms else None,
                          "peak_source": peak_src},
             "clocks": clk.summary()}
     if rank == 0:
@@ -872,7 +906,7 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
-    elif args.workload == "sssp":
+    elif args.workload in ("sssp", "cc"):
         run_sssp(args)
     else:
         run_b200(args)

@@ -306,6 +306,7 @@ GrB_Info GxB_b200_set_option(const char *name, int64_t value) {
     else if (!strcmp(name, "hub_mode")) g.hub_mode = value;
     else if (!strcmp(name, "red_flags")) g.red_flags = value;
     else if (!strcmp(name, "spgemm_panels")) g.spgemm_panels = value;
+    else if (!strcmp(name, "dot_hash")) g.dot_hash = value;
     else if (!strcmp(name, "panel_kb")) { if (value < 0) return GrB_INVALID_VALUE; g.panel_kb = value; }
     else if (!strcmp(name, "push_edge_ratio")) { if (value < 0) return GrB_INVALID_VALUE; g.push_edge_ratio = value; }
     else if (!strcmp(name, "smem_kb")) { if (value < 64 || value > 226) return GrB_INVALID_VALUE; g.smem_kb = value; }

@@ -154,6 +154,7 @@ struct GrbGlobal {
     int64_t smem_kb = 194;         // shared-memory budget of the hub-table kernels: <= 195 KB keeps the 196 KB carve-out, i.e. 60 KB of L1
                                    // for gather misses in flight (228 KB carve-out: 28 KB L1, gathers 1.5x slower, tools/microbench/gather_bench5)
     int64_t red_flags = 0;         // k_spmv_red: bit 0 = direct loads instead of TMA bulk copies (A/B measurements)
+    int64_t dot_hash = 1;          // masked dot product with a pair multiply: per-row hash sets instead of binary searches
     int64_t spgemm_panels = 1;     // SpGEMM heavy rows: shared-memory column panels (0 = per-CTA dense accumulator rows in HBM)
     int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
     // scratch

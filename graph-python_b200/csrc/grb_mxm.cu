@@ -263,6 +263,22 @@ __global__ void k_dot_compact(const uint8_t *has, const int64_t *pos, const uint
     Tj[o] = Mj[e]; Tx[o] = val[e];
 }
 
+// hash sets of the rows of R longer than DOT_HASH_MIN (grb_spgemm.cuh); caller frees off and tab
+static void build_row_hashes(const Csr &R, int64_t *&off, uint32_t *&tab) {
+    int64_t *sizes = dalloc<int64_t>(R.nrows + 1);
+    off = dalloc<int64_t>(R.nrows + 1);
+    GRB_LAUNCH("rowhash_sizes", k_rowhash_sizes, nblk(R.nrows), 256, 0, R.rowptr, R.nrows, sizes);
+    const int64_t total = scan_counts(sizes, off, R.nrows);
+    dfree(sizes);
+    tab = dalloc<uint32_t>(total);
+    if (total > 0) {
+        CUDA_TRY(cudaMemsetAsync(tab, 0xFF, (size_t)total * sizeof(uint32_t), g.stream));
+        uint32_t *rowid = csr_row_ids(R);
+        GRB_LAUNCH("rowhash_build", k_rowhash_build, nblk(R.nnz), 256, 0, rowid, R.colidx, R.nnz, off, tab);
+        dfree(rowid);
+    }
+}
+
 template <class T>
 static void dot_typed(const Csr &M, int m_vsize, int m_fp, const Csr &A, const Csr &Bt, int mon, int mul, int tcode, Csr &Tout) {
     const int64_t mnnz = M.nnz;
@@ -276,7 +292,18 @@ static void dot_typed(const Csr &M, int m_vsize, int m_fp, const Csr &A, const C
     d.Ap = A.rowptr; d.Aj = A.colidx; d.Ax = (const T *)A.vals; d.a_iso = A.iso;
     d.Bp = Bt.rowptr; d.Bj = Bt.colidx; d.Bx = (const T *)Bt.vals; d.b_iso = Bt.iso;
     d.val = val; d.has = has;
-    if (!gemm_launch_dot(mon, mul, tcode, &d, mnnz)) {
+    // multiplies that read no values (pair): membership through per-row hash sets instead of binary searches
+    int64_t *ah_off = nullptr, *bh_off = nullptr; uint32_t *ah_tab = nullptr, *bh_tab = nullptr;
+    d.Ah_off = d.Bh_off = nullptr; d.Ah_tab = d.Bh_tab = nullptr;
+    if (mul == OP_ONEB && g.dot_hash && mnnz > 0) {
+        build_row_hashes(A, ah_off, ah_tab);
+        d.Ah_off = ah_off; d.Ah_tab = ah_tab;
+        if (Bt.rowptr == A.rowptr && Bt.colidx == A.colidx) { d.Bh_off = ah_off; d.Bh_tab = ah_tab; }   // L.mxm(L.T): one set
+        else { build_row_hashes(Bt, bh_off, bh_tab); d.Bh_off = bh_off; d.Bh_tab = bh_tab; }
+    }
+    const bool dot_ok = gemm_launch_dot(mon, mul, tcode, &d, mnnz);
+    dfree(ah_off); dfree(ah_tab); dfree(bh_off); dfree(bh_tab);
+    if (!dot_ok) {
         dfree(mrow); dfree(val); dfree(has);
         grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel");
     }

@@ -74,13 +74,13 @@ def spgemm(A, op=None):
     return C, {"nnz_C": C.nvals}
 
 
-def cc_min_label(A, max_iters=None):
+def cc_min_label(A, max_iters=None, f0=None):
     """Connected components by min-label propagation with the FastSV product `mngp << A.mxv(gp, min_second)`
     (notebooks/Connected Components -- FastSV.ipynb cell 30).  FastSV's hooking / shortcutting steps need
     assign-by-index and extract (SURVEY 8f "next"); this loop keeps the product and the element-wise min, which is the
     part BASELINE config 5b measures (GTEPS = iterations x nnz / time)."""
     n = A.nrows
-    f = Vector.from_dense(np.arange(n, dtype=np.uint32))
+    f = f0.dup() if f0 is not None else Vector.from_dense(np.arange(n, dtype=np.uint32))   # f0: device-resident 0..n-1
     iters = 0
     max_iters = max_iters or n
     while iters < max_iters:

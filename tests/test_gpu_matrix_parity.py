@@ -202,6 +202,28 @@ def test_triangle_count_masked_dot(gb):
     assert int(gC.reduce_scalar().value) == int(np.trace(dense @ dense @ dense) // 6)
 
 
+@pytest.mark.parametrize("dot_hash", [1, 0])
+def test_masked_dot_pair_row_hash_sets(gb, dot_hash):
+    """Masked dot product with a pair multiply on two DIFFERENT operands with long rows: membership through per-row hash
+    sets (dot_hash = 1) and through binary searches (0) give the oracle's bits, for plus_pair and any_pair."""
+    rng = np.random.default_rng(11)
+    m, k, n = 300, 5000, 280
+    A = _rand_mat(rng, m, k, m * 200, "INT64")         # rows of ~200 entries (> 32: hashed)
+    B = _rand_mat(rng, k, n, k * 12, "INT64")          # columns of ~210 entries
+    M = _rand_mat(rng, m, n, 20000, "INT64")
+    gA, gB, gM = to_gpu_matrix(gb, A), to_gpu_matrix(gb, B), to_gpu_matrix(gb, M)
+    empty = O.Mat.from_coo([], [], np.zeros(0, dtype=np.int64), m, n, "INT64")
+    gb.set_option("dot_hash", dot_hash)
+    try:
+        for mon in ("PLUS", "ANY"):
+            ref = O.mxm(empty, A, B, mon, "PAIR", "INT64", mask=M, structure=True, method="dot")
+            gC = gb.Matrix("INT64", m, n)
+            gC(gM.S) << gA.mxm(gB, _sr(mon, "PAIR"))
+            assert mat_equal(gC, ref), (mon, gb.last_kernel())
+    finally:
+        gb.set_option("dot_hash", 1)
+
+
 def test_transpose_ewise_select_vs_oracle(gb):
     from graphblas_b200 import binary
 
