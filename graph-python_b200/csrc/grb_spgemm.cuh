@@ -620,6 +620,27 @@ __device__ __forceinline__ bool rowhash_has(const uint32_t *tab, int64_t o, uint
     }
 }
 
+// hits among sc[sp], sc[sp + stride], ... (up to U entries below se): the U first probes are issued together, the
+// rare collision chains are followed afterwards -- a probe is one random L2 / HBM sector, so loads in flight are the lever
+template <int U>
+__device__ __forceinline__ int rowhash_hits(const uint32_t *tab, int64_t o, uint32_t mask, const uint32_t *sc, int64_t sp,
+                                            int64_t se, int64_t stride) {
+    uint32_t key[U], h[U], v[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) { key[u] = (sp + u * stride < se) ? sc[sp + u * stride] : 0u; h[u] = (key[u] * 2654435761u) & mask; }
+#pragma unroll
+    for (int u = 0; u < U; u++) v[u] = (sp + u * stride < se) ? tab[o + h[u]] : HASH_EMPTY;
+    int hits = 0;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        if (sp + u * stride >= se) continue;
+        uint32_t hh = h[u], vv = v[u];
+        while (vv != key[u] && vv != HASH_EMPTY) { hh = (hh + 1) & mask; vv = tab[o + hh]; }
+        hits += vv == key[u];
+    }
+    return hits;
+}
+
 constexpr int DOT_THREADS = 256;
 constexpr int DOT_SERIAL_MAX = 32;   // a thread handles the pair alone if the shorter row has <= this many entries
 
@@ -655,11 +676,10 @@ __global__ void __launch_bounds__(DOT_THREADS) k_dot_masked(DotArgs<typename SR:
                         if (hs) {
                             const uint32_t *tab = a_short ? a.Bh_tab : a.Ah_tab;
                             const T one = SR::mult((T)0, (T)0);
-                            for (; sp < se; sp++) {
-                                if (rowhash_has(tab, ho, (uint32_t)hs - 1, sc[sp])) {
-                                    acc = has ? Mon::apply(acc, one) : one; has = true;
-                                    if (Mon::kAny) break;
-                                }
+                            for (; sp < se; sp += 4) {
+                                const int hits = rowhash_hits<4>(tab, ho, (uint32_t)hs - 1, sc, sp, se, 1);
+                                for (int c = 0; c < hits; c++) { acc = has ? Mon::apply(acc, one) : one; has = true; }
+                                if (Mon::kAny && has) break;
                             }
                             sp = se;       // done: skip the search loop below
                         }
@@ -702,8 +722,10 @@ __global__ void __launch_bounds__(DOT_THREADS) k_dot_masked(DotArgs<typename SR:
                     hashed = true;
                     const uint32_t *tab = a_short ? a.Bh_tab : a.Ah_tab;
                     const T one = SR::mult((T)0, (T)0);
-                    for (int64_t sp = ss + lane; sp < se; sp += 32)
-                        if (rowhash_has(tab, ho, (uint32_t)hs - 1, sc[sp])) { acc = has ? Mon::apply(acc, one) : one; has = true; }
+                    for (int64_t sp = ss + lane; sp < se; sp += 128) {
+                        const int hits = rowhash_hits<4>(tab, ho, (uint32_t)hs - 1, sc, sp, se, 32);
+                        for (int c = 0; c < hits; c++) { acc = has ? Mon::apply(acc, one) : one; has = true; }
+                    }
                 }
             }
         }
