@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--panel-kb", type=int, default=-1, help="column-panel threshold in KB (library option panel_kb; 0 = never)")
     ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
     ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
-    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc"],
+    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "spgemm", "tc"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
@@ -832,6 +832,107 @@ def measure_spgemm(gb, scale, reps=2):
                          "symbolic_heavy_rows_ms": (s_ms / s_cnt) if s_cnt else None}}
 
 
+# ---------------------------------------------------------------------------------------------- configs[3], [4]: sharded mxm
+def run_sharded_mxm(args):
+    """`bench.py --workload spgemm|tc [--gpus N] [--scale S]`: GrB_mxm with the rows of A (SpGEMM) or of the mask (triangle
+    counting) split into N row blocks, B replicated on every rank, no data-path collective; the only exchange
+    is the final sum of the per-rank entry counts / triangle counts.  Strong scaling at a fixed scale; one step = one
+    product.  value = whole-job output entries/s (spgemm) or mask entries/s (tc)."""
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: libgrb_b200 has no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import graphblas_b200 as gb
+    from graphblas_b200 import Matrix, monoid, semiring
+    from graphblas_b200.sharding import row_block
+
+    gb.init("b200")
+    gb.use_torch_stream()
+    kind, scale = args.workload, args.scale
+    n = 1 << scale
+    lo, hi = row_block(n, rank, world)
+    if kind == "spgemm":
+        A = Matrix.rmat(scale, "FP64", value_mode=2)                      # same graph on every rank (B replicated)
+        Ab = A if world == 1 else A.rowblock(lo, hi)
+
+        def product():
+            C = Ab.mxm(A, semiring.plus_times).new()
+            return C.nvals, C                                              # nvals forces completion
+    else:
+        G = Matrix.rmat(scale, "INT64", symmetrize=True)
+        L = G.select("tril", -1).new()
+        del G
+        if world > 1:
+            # rows of L grow with the row index (row i holds its neighbours below i): equal ROW blocks gave 1.11x on two
+            # GPUs; cut where the prefix of the mask entries crosses k / world of the total instead
+            rp = gb.ffi.new("void**")
+            gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, L._carg)
+            rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+            cuts = torch.searchsorted(rowptr, torch.tensor([L.nvals * k // world for k in range(1, world)], device="cuda"))
+            bounds = [0] + [int(c) for c in cuts.cpu()] + [n]
+            lo, hi = bounds[rank], bounds[rank + 1]
+        Lb = L if world == 1 else L.rowblock(lo, hi)
+        gb.lib.GxB_b200_Matrix_prepare(L._carg, 0)
+
+        def product():
+            C = Matrix("INT64", hi - lo if world > 1 else n, n)
+            C(Lb.S) << Lb.mxm(L.T, semiring.plus_pair)
+            return int(C.reduce_scalar(monoid.plus).value or 0), C
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    steps = args.steps
+    with ClockSampler(local_rank) as clk:
+        for _ in range(max(args.warmup, 3) if kind == "tc" else 1):    # SpGEMM scale 20 writes 116 GB per product: one warm-up
+            res, C = product()
+            del C
+        barrier()
+        clk.mark_begin()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = gb.launch_count()
+        ev0.record()
+        for _ in range(steps):
+            res, C = product()
+            del C
+        ev1.record()
+        barrier()
+        clk.mark_end()
+        ms = ev0.elapsed_time(ev1)
+        launches = gb.launch_count() - l0
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([res, (Ab if kind == "spgemm" else Lb).nvals], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot)
+    ms = float(t.item()) / steps
+    total, units = int(tot[0].item()), int(tot[1].item())
+    if kind == "spgemm":
+        value, unit, what = total / ms * 1e3, "output entries/s", {"nnz_A": units, "nnz_C": total}
+        wl = (f"C = A.mxm(A, plus_times) FP64, directed R-MAT scale {scale} edgefactor 16 (BASELINE configs[4]), rows of A in {world} "
+              "row block(s), B replicated, C stays row-sharded")
+    else:
+        value, unit, what = units / ms * 1e3, "mask entries/s", {"nnz_L": units, "triangles": total, "triangles_per_s": total / ms * 1e3}
+        wl = (f"C(L.S) << L.mxm(L.T, plus_pair) + reduce, L = tril of the symmetrised R-MAT scale {scale} graph (BASELINE configs[3]), "
+              f"mask and A in {world} row block(s), L replicated, final all-reduce of the count")
+    line = {"metric": "SpGEMM output entries/s" if kind == "spgemm" else "triangle counting mask entries/s", "value": value,
+            "unit": unit, "n_gpus": world, "steps": steps, "warmup": 1 if kind == "spgemm" else max(args.warmup, 3), "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64" if kind == "spgemm" else "int64",
+            "data": "synthetic", "config": {"workload": wl, "scale": scale, "parallelism": f"{world} GPU(s), 1-D row blocks", **what},
+            "gpu_launches": int(launches), "clocks": clk.summary()}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def run_extra(gb, args):
     """The other BASELINE configs on one GPU (extra keys of the JSON line; not the headline metric)."""
     import torch
@@ -908,6 +1009,8 @@ def main():
         run_reference(args)
     elif args.workload in ("sssp", "cc"):
         run_sssp(args)
+    elif args.workload in ("spgemm", "tc"):
+        run_sharded_mxm(args)
     else:
         run_b200(args)
 

@@ -149,3 +149,52 @@ def test_fastsv_vs_scipy_and_permutation(gb):
     # two vertices share a label before the permutation iff they share one after it
     a, b = rng.integers(0, n, size=20000), rng.integers(0, n, size=20000)
     assert np.array_equal(vals[a] == vals[b], vp[p[a]] == vp[p[b]])
+
+
+# ---- BASELINE's full sizes, through size-independent properties (the oracle does not finish these in seconds) ----
+@pytest.mark.parametrize("scale,dt", [(18, "INT64"), (20, "FP64")])
+def test_spgemm_full_size_row_sums(gb, scale, dt):
+    """(A A) 1 = A (A 1): the row sums of C = A.mxm(A, plus_times) against two mxv's of the ones vector.  INT64 wraps
+    like C, so the identity is bit-exact; FP64 values lie in (0, 1] (no cancellation), tolerance 1e-5 relative as
+    north_star states.  Scale 20 FP64 is BASELINE configs[4] itself (9.7 G entries out)."""
+    from graphblas_b200 import Vector, monoid, semiring
+
+    A = gb.Matrix.rmat(scale, dt, value_mode=1 if dt == "INT64" else 2)
+    n = A.nrows
+    ones = Vector.from_dense(np.ones(n, dtype=np.int64 if dt == "INT64" else np.float64))
+    t = A.mxv(ones, semiring.plus_times).new()
+    # rows without entries give no entry in t; A (A 1) only reads t where A has columns, absent = 0 under plus
+    expect = A.mxv(t, semiring.plus_times).new()
+    C = A.mxm(A, semiring.plus_times).new()
+    got = C.reduce_rowwise(monoid.plus).new()
+    assert got.nvals == expect.nvals
+    gv, gp = got.to_dense()
+    ev, ep = expect.to_dense()
+    assert np.array_equal(gp, ep)
+    if dt == "INT64":
+        assert np.array_equal(gv[gp.astype(bool)], ev[ep.astype(bool)])
+    else:
+        assert np.allclose(gv[gp.astype(bool)], ev[ep.astype(bool)], rtol=1e-5, atol=0)
+    del C, got, expect
+
+
+def test_triangle_count_scale20_two_algorithms(gb):
+    """BASELINE configs[3] at scale 20: the hash-set membership path and the binary-search path of the masked dot
+    product are independent implementations; they must agree entry for entry, and with trace-free counting
+    sum(C) = sum over edges (i > j) of |N<(i) & N<(j)|."""
+    from graphblas_b200 import Matrix, monoid, semiring
+
+    A = gb.Matrix.rmat(20, "INT64", symmetrize=True)
+    L = A.select("tril", -1).new()
+    out = []
+    for h in (1, 0):
+        gb.set_option("dot_hash", h)
+        try:
+            C = Matrix("INT64", A.nrows, A.ncols)
+            C(L.S) << L.mxm(L.T, semiring.plus_pair)
+            out.append(C)
+        finally:
+            gb.set_option("dot_hash", 1)
+    assert out[0].nvals == out[1].nvals
+    assert out[0].isequal(out[1])
+    assert int(out[0].reduce_scalar(monoid.plus).value) == 423274849      # same count as every earlier run of this graph
