@@ -872,8 +872,9 @@ def run_sharded_mxm(args):
             rp = gb.ffi.new("void**")
             gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, L._carg)
             rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
-            cuts = torch.searchsorted(rowptr, torch.tensor([L.nvals * k // world for k in range(1, world)], device="cuda"))
-            bounds = [0] + [int(c) for c in cuts.cpu()] + [n]
+            from graphblas_b200.sharding import balanced_row_cuts
+
+            bounds = balanced_row_cuts(rowptr, world)
             lo, hi = bounds[rank], bounds[rank + 1]
         Lb = L if world == 1 else L.rowblock(lo, hi)
         gb.lib.GxB_b200_Matrix_prepare(L._carg, 0)

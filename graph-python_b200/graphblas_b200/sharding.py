@@ -25,6 +25,21 @@ def row_blocks(n, world):
     return [row_block(n, r, world) for r in range(world)]
 
 
+def balanced_row_cuts(rowptr, world):
+    """Row boundaries [0, c1, ..., n] that give every rank about nnz / world entries: rank r owns rows
+    [cuts[r], cuts[r+1]).  `rowptr` is a torch int64 tensor of n + 1 offsets (host or device).  Used where equal ROW
+    blocks are unbalanced by construction (the lower triangle L of triangle counting: row i holds its neighbours
+    below i, so rows grow with the index)."""
+    n = rowptr.numel() - 1
+    nnz = int(rowptr[-1].item())
+    targets = torch.tensor([nnz * k // world for k in range(1, world)], dtype=rowptr.dtype, device=rowptr.device)
+    cuts = torch.searchsorted(rowptr.contiguous(), targets) if world > 1 else targets
+    bounds = [0] + [min(int(c), n) for c in cuts.cpu()] + [n]
+    for k in range(1, len(bounds)):                      # monotone even for empty tails
+        bounds[k] = max(bounds[k], bounds[k - 1])
+    return bounds
+
+
 class BlockExchange:
     """All-gather of the ranks' vector blocks into every rank's full-length vector.
 

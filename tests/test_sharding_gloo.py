@@ -82,3 +82,116 @@ def test_sharded_pagerank_iteration_matches_single_process(tmp_path, n):
         O.mxv(rv, P, w, "PLUS", "TIMES", "FP32", accum="PLUS")
         r = rv.values
     assert np.array_equal(got, r)     # same per-row arithmetic in the same order: bit-identical
+
+
+# ---- the other sharded loops of bench.py (SsspJob, run_sharded_mxm) on CPU, world 2 over gloo ----
+from graphblas_b200.sharding import balanced_row_cuts
+
+
+def test_balanced_row_cuts():
+    rowptr = torch.tensor([0, 0, 1, 3, 6, 10, 15, 21, 28, 36, 45])       # row i holds i entries (a lower triangle)
+    assert balanced_row_cuts(rowptr, 1) == [0, 10]
+    b = balanced_row_cuts(rowptr, 2)
+    assert b[0] == 0 and b[-1] == 10 and 6 <= b[1] <= 8                 # half of 45 entries is reached inside row 6
+    b = balanced_row_cuts(rowptr, 4)
+    assert b == sorted(b) and len(b) == 5
+    sizes = [int(rowptr[b[k + 1]] - rowptr[b[k]]) for k in range(4)]
+    assert sum(sizes) == 45 and max(sizes) <= 45 // 4 + 9               # within one row of the ideal share
+    empty = torch.zeros(5, dtype=torch.int64)
+    assert balanced_row_cuts(empty, 3) == [0, 0, 0, 4] or balanced_row_cuts(empty, 3)[-1] == 4
+
+
+def _block(M, lo, hi):
+    return O.Mat(M.indptr[lo:hi + 1] - M.indptr[lo], M.indices[M.indptr[lo]:M.indptr[hi]],
+                 M.values[M.indptr[lo]:M.indptr[hi]], (hi - lo, M.shape[1]), M.dtype)
+
+
+def _sssp_worker(rank, world, port, scale, src, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = O.rmat_matrix(scale, "INT64", symmetrize=True, value_mode=1)
+        n = A.shape[0]
+        ex = BlockExchange(n)
+        lo, hi = ex.lo, ex.hi
+        Pb = _block(A.transpose(), lo, hi)
+        w = O.Vec.from_coo([src], [0], n, "INT64")
+        wb = O.Vec.from_coo([src - lo] if lo <= src < hi else [], [0] if lo <= src < hi else [], hi - lo, "INT64")
+        flag = torch.zeros(1, dtype=torch.int32)
+        iters = 0
+        while True:
+            prev = wb.dup()
+            O.mxv(wb, Pb, w, "MIN", "PLUS", "INT64", accum="MIN")
+            iters += 1
+            same = np.array_equal(prev.present, wb.present) and np.array_equal(prev.values[prev.present.astype(bool)],
+                                                                                wb.values[wb.present.astype(bool)])
+            flag.fill_(0 if same else 1)
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+            if int(flag.item()) == 0:
+                break
+            wv, wp = torch.zeros(n, dtype=torch.int64), torch.zeros(n, dtype=torch.uint8)
+            ex.all_gather(wv, torch.from_numpy(wb.values.astype(np.int64)))
+            ex.all_gather(wp, torch.from_numpy(wb.present.astype(np.uint8)))
+            w = O.Vec(wv.numpy().copy(), wp.numpy().copy(), "INT64")
+        if rank == 0:
+            np.savez(out, values=w.values, present=w.present, iters=iters)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_bellman_ford_matches_single_process(tmp_path):
+    scale, world = 9, 2
+    A = O.rmat_matrix(scale, "INT64", symmetrize=True, value_mode=1)
+    src = int(np.argmax(np.diff(A.indptr)))
+    out = str(tmp_path / "w.npz")
+    mp.spawn(_sssp_worker, args=(world, _free_port(), scale, src, out), nprocs=world, join=True)
+    got = np.load(out)
+    n = A.shape[0]
+    w = O.Vec.from_coo([src], [0], n, "INT64")
+    iters = 0
+    while True:
+        prev = w.dup()
+        O.vxm(w, w.dup(), A, "MIN", "PLUS", "INT64", accum="MIN")
+        iters += 1
+        if np.array_equal(prev.present, w.present) and np.array_equal(prev.values[prev.present.astype(bool)],
+                                                                       w.values[w.present.astype(bool)]):
+            break
+    p = w.present.astype(bool)
+    assert int(got["iters"]) == iters
+    assert np.array_equal(got["present"].astype(bool), p)
+    assert np.array_equal(got["values"][p], w.values[p])
+
+
+def _tc_worker(rank, world, port, scale, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = O.rmat_matrix(scale, "INT64", symmetrize=True, value_mode=0)
+        r, c, _ = A.to_coo()
+        n = A.shape[0]
+        L = O.Mat.from_coo(r[c < r], c[c < r], np.ones(int((c < r).sum()), dtype=np.int64), n, n, "INT64")
+        bounds = balanced_row_cuts(torch.from_numpy(L.indptr.astype(np.int64)), world)
+        lo, hi = bounds[rank], bounds[rank + 1]
+        Lb = _block(L, lo, hi)
+        empty = O.Mat.from_coo([], [], np.zeros(0, dtype=np.int64), hi - lo, n, "INT64")
+        C = O.mxm(empty, Lb, L, "PLUS", "PAIR", "INT64", mask=Lb, structure=True, tran1=True, method="dot")
+        tot = torch.tensor([int(C.values.sum()) if C.nnz else 0, Lb.nnz], dtype=torch.int64)
+        dist.all_reduce(tot)
+        if rank == 0:
+            np.save(out, tot.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_triangle_count_matches_single_process(tmp_path):
+    scale, world = 8, 2
+    out = str(tmp_path / "t.npy")
+    mp.spawn(_tc_worker, args=(world, _free_port(), scale, out), nprocs=world, join=True)
+    got = np.load(out)
+    A = O.rmat_matrix(scale, "INT64", symmetrize=True, value_mode=0)
+    n = A.shape[0]
+    dense = np.zeros((n, n), dtype=np.int64)
+    r, c, _ = A.to_coo()
+    dense[r, c] = 1
+    assert int(got[0]) == int(np.trace(dense @ dense @ dense) // 6)
+    assert int(got[1]) == A.nnz // 2
