@@ -118,20 +118,18 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *total, int *s_wa
 
 // Emit a shared-memory hash table in key order without sorting the table: keys are dealt into nbk order-preserving
 // buckets ((key - min) >> shift, about 8 entries each), a counting pass places slot numbers bucket by bucket, one
-// thread orders each bucket by insertion, and the row leaves through coalesced stores.  O(table) work against the
-// O(table log^2 table) of a bitonic sort (measured: 140 us -> a few us per 16 K-slot table).  A bucket with more
-// than HASH_BUCKET_MAX entries (clustered keys) falls back to the bitonic sort.  Returns the entry count.
+// thread per entry ranks it inside its bucket, and the row leaves in order.  O(table) work against the
+// O(table log^2 table) of a bitonic sort (measured: 140 us -> a few us per 16 K-slot table); clustered keys cost
+// O(bucket^2) compares spread over the bucket's threads.  Returns the entry count.
 //   slot: >= (entries) uint16;  bpos: >= nbk uint32;  s_tmp: >= 40 ints;  nbk a power of two
-constexpr int HASH_BUCKET_MAX = 48;
 template <class T> __device__ __forceinline__ T ld_acc(const T *p, bool global_vals) { return global_vals ? *(const volatile T *)p : *p; }
 template <class T, bool GV = false>
 __device__ __forceinline__ int hash_emit_sorted(uint32_t *keys, T *vals, int table, uint16_t *slot, uint32_t *bpos, int nbk,
                                                 uint32_t *Cj, T *Cx, int64_t out, int *s_tmp) {
     const int tid = threadIdx.x, nthreads = blockDim.x, lane = tid & 31;
     uint32_t *s_min = (uint32_t *)&s_tmp[33], *s_max = (uint32_t *)&s_tmp[34];
-    int *s_flag = &s_tmp[35];
     for (int b = tid; b < nbk; b += nthreads) bpos[b] = 0;
-    if (tid == 0) { *s_min = 0xFFFFFFFFu; *s_max = 0; *s_flag = 0; }
+    if (tid == 0) { *s_min = 0xFFFFFFFFu; *s_max = 0; }
     __syncthreads();
     uint32_t lo = 0xFFFFFFFFu, hi = 0;
     for (int k = tid; k < table; k += nthreads) { const uint32_t key = keys[k]; if (key != HASH_EMPTY) { lo = min(lo, key); hi = max(hi, key); } }
@@ -157,24 +155,19 @@ __device__ __forceinline__ int hash_emit_sorted(uint32_t *keys, T *vals, int tab
         if (key != HASH_EMPTY) slot[atomicAdd(&bpos[(key - lo) >> sh], 1u)] = (uint16_t)k;
     }
     __syncthreads();
-    // bpos[b] is now the end of bucket b
-    for (int b = tid; b < nbk; b += nthreads) {
+    // bpos[b] is now the end of bucket b.  One thread per ENTRY: its rank inside its bucket is the number of smaller
+    // keys there (keys of a row are distinct), which is its output position -- ordering and emission in one pass, spread
+    // over all threads whatever the bucket sizes are (one thread ordering each bucket by insertion was 11 % of the
+    // instructions of k_panel_row and left a clustered bucket to a single thread).
+    for (int p = tid; p < total; p += nthreads) {
+        const int sl = slot[p];
+        const uint32_t key = keys[sl];
+        const uint32_t b = (key - lo) >> sh;
         const int beg = b ? (int)bpos[b - 1] : 0, end = (int)bpos[b];
-        if (end - beg > HASH_BUCKET_MAX) { *s_flag = 1; continue; }
-        for (int i = beg + 1; i < end; i++) {
-            const uint16_t si = slot[i];
-            const uint32_t ki = keys[si];
-            int j = i - 1;
-            while (j >= beg && keys[slot[j]] > ki) { slot[j + 1] = slot[j]; j--; }
-            slot[j + 1] = si;
-        }
-    }
-    __syncthreads();
-    if (*s_flag) {
-        bitonic_sort<T, false>(keys, vals, table, tid, nthreads);
-        for (int k = tid; k < total; k += nthreads) { Cj[out + k] = keys[k]; Cx[out + k] = ld_acc(&vals[k], GV); }
-    } else {
-        for (int k = tid; k < total; k += nthreads) { const int sl = slot[k]; Cj[out + k] = keys[sl]; Cx[out + k] = ld_acc(&vals[sl], GV); }
+        int rank = 0;
+        for (int j = beg; j < end; j++) rank += keys[slot[j]] < key;
+        Cj[out + beg + rank] = key;
+        Cx[out + beg + rank] = ld_acc(&vals[sl], GV);
     }
     return total;
 }
