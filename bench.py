@@ -47,6 +47,10 @@ def parse_args():
     ap.add_argument("--panel-kb", type=int, default=-1, help="column-panel threshold in KB (library option panel_kb; 0 = never)")
     ap.add_argument("--smem-kb", type=int, default=0, help="shared-memory budget of the hub-table kernels (library option smem_kb)")
     ap.add_argument("--red-flags", type=int, default=0, help="k_spmv_red experiment switches (1: no TMA; 2, 4: timing-only ablations)")
+    ap.add_argument("--ag-chunks", type=int, default=0,
+                    help="N > 1: split every rank's block of w into this many chunks, one all-gather per chunk, and pull chunk c "
+                         "(its own column-permuted slice of the row block) while chunk c+1 is still in flight; 1 = one all-gather, "
+                         "then one pull; 0 = auto (4 from 8 GPUs on, else 1: measured +3 %% at N = 8, -14 %% at N = 2)")
     ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "spgemm", "tc"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
@@ -256,7 +260,7 @@ def kernel_time(gb, name):
 class PageRankJob:
     """Device-resident state of one rank: its row block of the pull matrix, the full-length w, and r / d blocks."""
 
-    def __init__(self, gb, scale, rank, world):
+    def __init__(self, gb, scale, rank, world, chunks=1):
         import torch
         from graphblas_b200 import Matrix, Vector
 
@@ -284,6 +288,9 @@ class PageRankJob:
             self.P, self.transposed = AT.rowblock(self.lo, self.hi), False
             del AT, A
         self.nnz_local = self.P.nvals
+        self.chunks = 1
+        if world > 1 and chunks > 1 and nb % chunks == 0 and n % world == 0:
+            self._split_columns(chunks)
         self.d = Vector.from_dense(d[self.lo:self.hi].cpu().numpy())
         self.r = Vector.from_dense(np.full(nb, 1.0 / n, dtype=np.float32))
         self.wb = Vector.from_dense(np.zeros(nb, dtype=np.float32))
@@ -291,7 +298,40 @@ class PageRankJob:
         self.teleport = float(np.float32((1 - DAMPING) / n))
         if world > 1:
             self.wb_t, self.w_t = vector_tensor(gb, self.wb), vector_tensor(gb, self.w)
+            if self.chunks > 1:
+                self.stage = [Vector.from_dense(np.zeros(n // self.chunks, dtype=np.float32)) for _ in range(self.chunks)]
+                self.stage_t = [vector_tensor(gb, v) for v in self.stage]
         gb.sync()
+
+    def _split_columns(self, C):
+        """Cut this rank's row block P (nb x n) into C matrices P_c (nb x n/C): P_c holds the columns that lie in chunk c of
+        their owner's block, renumbered owner * (nb/C) + offset -- the layout one all-gather of the ranks' c-th chunks
+        produces.  Rows stay sorted (the renumbering is monotone inside a chunk), products are unchanged; the pull over
+        P_c can start when chunk c has arrived, while the later chunks are still on the wire."""
+        import torch
+        from graphblas_b200 import Matrix
+
+        gb, n, nb = self.gb, self.n, self.hi - self.lo
+        nbc = nb // C
+        rp, ci, vx = gb.ffi.new("void**"), gb.ffi.new("void**"), gb.ffi.new("void**")
+        gb.lib.GxB_b200_Matrix_device_ptrs(rp, ci, vx, self.P._carg)
+        nnz = self.P.nvals
+        rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), nb + 1, "<i8")
+        col = dev_tensor(int(gb.ffi.cast("uintptr_t", ci[0])), nnz, "<i4").to(torch.int64)
+        val = dev_tensor(int(gb.ffi.cast("uintptr_t", vx[0])), nnz, "<f4")
+        row = torch.repeat_interleave(torch.arange(nb, device="cuda"), rowptr[1:] - rowptr[:-1])
+        owner, within = col // nb, col % nb
+        chunk, newcol = within // nbc, owner * nbc + within % nbc
+        parts = []
+        for c in range(C):
+            m = chunk == c
+            counts = torch.bincount(row[m], minlength=nb)
+            indptr = torch.zeros(nb + 1, dtype=torch.int64, device="cuda")
+            indptr[1:] = torch.cumsum(counts, 0)
+            parts.append(Matrix.from_csr(indptr.cpu().numpy(), newcol[m].cpu().numpy(), val[m].cpu().numpy(), dtype="FP32",
+                                         ncols=n // C, nrows=nb))
+        assert sum(p.nvals for p in parts) == nnz
+        self.Pc, self.chunks = parts, C          # self.P (the unsplit block) stays for the e2e leg's host export
 
     def reset(self):
         self.r[:] << 1.0 / self.n
@@ -302,6 +342,17 @@ class PageRankJob:
         import torch.distributed as dist
         from graphblas_b200 import binary, semiring
 
+        if self.chunks > 1:
+            C, nbc = self.chunks, (self.hi - self.lo) // self.chunks
+            for _ in range(ITERS):
+                self.wb << self.r.ewise_mult(self.d, binary.truediv)
+                works = [dist.all_gather_into_tensor(self.stage_t[c], self.wb_t[c * nbc:(c + 1) * nbc], async_op=True)
+                         for c in range(C)]
+                self.r[:] << self.teleport
+                for c in range(C):
+                    works[c].wait()                    # the compute stream waits for chunk c only
+                    self.r(binary.plus) << self.Pc[c].mxv(self.stage[c], semiring.plus_times)
+            return
         P = self.P.T if self.transposed else self.P
         for _ in range(ITERS):
             self.wb << self.r.ewise_mult(self.d, binary.truediv)
@@ -488,7 +539,7 @@ def run_b200(args):
     if args.panel_kb >= 0:
         gb.set_option("panel_kb", args.panel_kb)
     scale = args.scale + int(np.log2(world))
-    job = PageRankJob(gb, scale, rank, world)
+    job = PageRankJob(gb, scale, rank, world, args.ag_chunks or (4 if world >= 8 else 1))
     nnz = job.nnz_total
 
     def barrier():
@@ -535,7 +586,8 @@ def run_b200(args):
     nb = job.hi - job.lo
     alg_bytes = job.nnz_local * (4 + 4 + 4) + nb * (8 + 4 + 4)   # nnz*(I+V+X) + n*(P+Y) + accum read n*Y
     peak, peak_src = measured_peaks()
-    achieved = alg_bytes / (k_ms / max(k_cnt, 1) * 1e-3) / 1e9 if k_cnt else None
+    products = args.steps * ITERS                  # one product = 1 launch at N = 1, one per column panel / chunk at N > 1
+    achieved = alg_bytes * products / (k_ms * 1e-3) / 1e9 if k_cnt else None
     line = {
         "metric": METRIC, "value": value, "unit": "GTEPS", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -545,7 +597,8 @@ def run_b200(args):
                      "unit": "GB/s", "frac": (achieved / peak) if achieved else None, "traffic": None,
                      "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)" if peak_src == "measured" else "fallback 6650",
                      "algorithmic_bytes_per_launch": int(alg_bytes), "avg_launch_ms": k_ms / max(k_cnt, 1),
-                     "launches_timed": k_cnt, "kernel_share_of_step": (k_ms / ms) if ms else None},
+                     "launches_timed": k_cnt, "launches_per_product": k_cnt / max(products, 1),
+                     "kernel_share_of_step": (k_ms / ms) if ms else None},
     }
     traffic_file = os.path.join(ROOT, "profiles", "spmv_pull_traffic.json")
     if os.path.exists(traffic_file):
@@ -554,6 +607,13 @@ def run_b200(args):
         except Exception:
             pass
     line["clocks"] = clk.summary()
+    if world > 1:
+        # the result of the last step, reduced over the ranks: the same for every --ag-chunks setting up to FP32 rounding
+        rt = vector_tensor(gb, job.r).double()
+        chk = torch.stack([rt.sum(), (rt * rt).sum()])
+        dist.all_reduce(chk)
+        line["config"]["ag_chunks"] = job.chunks
+        line["config"]["rank_sum"], line["config"]["rank_sumsq"] = float(chk[0].item()), float(chk[1].item())
     if rank == 0 and world == 1:
         r_dev, _ = job.r.to_dense()
         if not args.no_e2e:
