@@ -180,16 +180,20 @@ __device__ __forceinline__ int hash_emit_sorted(uint32_t *keys, T *vals, int tab
 // the stall samples of the first version sat on that barrier).
 // (Flattening the 32 segments of a warp with a scan + shuffle search was measured 1.4-4x SLOWER on R-MAT: the search
 // costs more than the idle lanes it saves.)
-constexpr int SEGQ_CAP = 384;
-struct SegQueue { long long s0[SEGQ_CAP]; int len[SEGQ_CAP]; int poff[SEGQ_CAP]; int n[2]; };
+// queue capacity: 384 for the 1024-thread heavy-row kernels; 64 for the 64..512-thread hash-row kernel, whose occupancy the
+// 6 KB of a large queue would cut (mid-size rows 35.7 -> 27.8 ms at scale 20 with a smaller queue)
+template <int CAP> struct SegQueueT { static constexpr int kCap = CAP; long long s0[CAP]; int len[CAP]; int poff[CAP]; int n[2]; };
+using SegQueue = SegQueueT<384>;
+using SegQueueSmall = SegQueueT<64>;
 // ld(pA, qB) loads one product (column + value), put(prod) accumulates it.  The two are split so that PANEL_UNROLL loads
 // are in flight per thread before the first shared-memory atomic: the compiler cannot move loads across atomics itself.
 // PANEL_UNROLL = products loaded ahead of their inserts: 4 pays in the symbolic pass (8.5 vs 10.5 ms), not in the numeric one.
 // PANEL_SHORT: a lane walks a B segment of up to this many entries alone; above PANEL_LONG a segment goes to the CTA queue
 // (1024-thread CTAs: 8 / 8, i.e. everything that is not tiny is shared -- 83 -> 64 ms; 64..512-thread CTAs: 16 / 64).
-template <int PANEL_UNROLL, int PANEL_SHORT, int PANEL_LONG, class LD, class PUT>
+template <int PANEL_UNROLL, int PANEL_SHORT, int PANEL_LONG, class Q, class LD, class PUT>
 __device__ __forceinline__ void panel_products(const int64_t *Ap, const uint32_t *Aj, const int64_t *Bp, int64_t row,
-                                               const uint32_t *ptab, int np, int q0, int q1, SegQueue *sq, LD &&ld, PUT &&put) {
+                                               const uint32_t *ptab, int np, int q0, int q1, Q *sq, LD &&ld, PUT &&put) {
+    constexpr int SEGQ_CAP = Q::kCap;
     using Prod = decltype(ld((int64_t)0, (int64_t)0));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;   // nwarps: a power of two
     const int64_t pb = Ap[row], pe = Ap[row + 1];
@@ -309,7 +313,7 @@ __global__ void k_hash_block(GemmArgs<typename SR::type> a, int table) {
     T *vals = (T *)(smem_raw + (size_t)table * sizeof(uint32_t));
     __shared__ int s_cnt;
     __shared__ int s_tmp[40];
-    __shared__ SegQueue s_q;
+    __shared__ SegQueueSmall s_q;
     const int tid = threadIdx.x, nthreads = blockDim.x, lane = tid & 31;
     const int64_t row = a.rows[blockIdx.x];
     for (int k = tid; k < table; k += nthreads) { keys[k] = HASH_EMPTY; if (NUMERIC) vals[k] = SR::Mon::identity(); }
@@ -395,8 +399,8 @@ __global__ void k_dense_block(GemmArgs<typename SR::type> a) {
 
 // ---- heavy rows: column panels, accumulators in shared memory ----
 // One 1024-thread CTA per SM around a 16 K-slot table.  (Four 256-thread CTAs per SM with 4 K-slot tables were measured
-// 25 % slower on R-MAT scale 18-20: four times as many ranges, each re-walking the A row, cost more than the overlap of
-// the barrier-separated phases gains.)
+// 25 % slower on R-MAT scale 18-20, two 512-thread CTAs with 8 K-slot tables 12 % slower at scale 20 (425 vs 378 ms): more
+// ranges, each re-walking the A row, cost more than the overlap of the barrier-separated phases gains.)
 constexpr int PANEL_W = 16384;                  // columns per base panel = entries of the dense accumulator
 constexpr int PANEL_TABLE = PANEL_W;            // hash slots per range
 constexpr int PANEL_CAP = PANEL_W / 2;          // entries a range may hold (load factor 0.5)
