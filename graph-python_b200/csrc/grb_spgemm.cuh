@@ -403,7 +403,7 @@ __global__ void k_dense_block(GemmArgs<typename SR::type> a) {
 // ranges, each re-walking the A row, cost more than the overlap of the barrier-separated phases gains.)
 constexpr int PANEL_W = 16384;                  // columns per base panel = entries of the dense accumulator
 constexpr int PANEL_TABLE = PANEL_W;            // hash slots per range
-constexpr int PANEL_CAP = PANEL_W / 2;          // entries a range may hold (load factor 0.5)
+constexpr int PANEL_CAP = PANEL_W / 2;          // entries a range may hold: load factor 0.5 (0.375: 402 ms, 0.75: 435 ms, 0.5: 378 ms at scale 20)
 constexpr int PANEL_NBK = PANEL_TABLE / 8;      // buckets of the ordered emission
 constexpr int PANEL_THREADS = PANEL_W / 16;     // the dense extraction gives every thread 16 columns
 constexpr int PANEL_CTAS_PER_SM = 1;
@@ -477,7 +477,7 @@ static __global__ void __launch_bounds__(PSYM_THREADS, 1) k_panel_symbolic(GemmA
             int best = -1;
             for (int g = 8; g >= 0; g--) { const int mx = warp_max(m[g]); if (best < 0 && mx <= PANEL_CAP) best = g; }
             // ranges of one base panel always take the dense accumulator (it holds any count and needs no hashing)
-            if (lane == 0) { a.rownnz[row] = total; a.rowS[row] = best < 1 ? (uint16_t)1 : (uint16_t)(1u << best); }
+            if (lane == 0) { a.rownnz[row] = total; a.rowS[row] = best < 2 ? (uint16_t)1 : (uint16_t)(1u << best); }
         }
         __syncthreads();
     }
