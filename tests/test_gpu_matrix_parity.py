@@ -84,10 +84,11 @@ def test_spgemm_hub_rows_dense_path(gb):
     assert mat_equal(gC, T)
 
 
-@pytest.mark.parametrize("panels", [1, 0])
+@pytest.mark.parametrize("panels", [1, 2, 0])
 def test_spgemm_heavy_rows_hash_ranges(gb, panels):
     """Heavy rows whose columns are cut into several shared-memory hash ranges or dense base panels (25 base panels
-    of 4 K columns), next to the HBM dense-accumulator fallback (spgemm_panels = 0): same bits either way."""
+    of 4 K columns), next to the variant that keeps the values in an L2-resident buffer (2) and the HBM dense-accumulator fallback
+    (spgemm_panels = 0): same bits every way."""
     rng = np.random.default_rng(7)
     n = 100000
     B = _rand_mat(rng, n, n, n * 100, "FP64")
