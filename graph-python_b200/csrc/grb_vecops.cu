@@ -249,3 +249,40 @@ GrB_Info GxB_Vector_Option_get_INT32(GrB_Vector v, GxB_Option_Field field, int32
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------- fused isequal
+// What python-graphblas's Vector.isequal computes with eWiseMult(eq) + nvals + reduce(land) (reference
+// graphblas/core/vector.py isequal -> core/base.py _isequal), i.e. four host synchronisations per call, in one pass and
+// one read-back: same pattern, and `eq` true on every common entry.  The fixed-point loops (Bellman-Ford, FastSV) call
+// it every iteration.
+template <class T>
+__global__ void __launch_bounds__(256) k_vec_isequal(const T *uv, const uint8_t *up, const T *vv, const uint8_t *vp, int64_t n, int *differ) {
+    bool d = false;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const bool pu = up[i] != 0, pv = vp[i] != 0;
+        d |= (pu != pv) || (pu && !(uv[i] == vv[i]));
+    }
+    if (__any_sync(0xffffffffu, d) && (threadIdx.x & 31) == 0) *differ = 1;
+}
+
+extern "C" GrB_Info GxB_b200_Vector_isequal(bool *result, const GrB_Vector u_, const GrB_Vector v_) {
+    if (!result) return GrB_NULL_POINTER;
+    API_BEGIN
+    require_init();
+    GB_Object *u = obj_check(u_, "u"), *v = obj_check(v_, "v");
+    if (u->kind == K_MATRIX || v->kind == K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "isequal: needs vectors");
+    if (u->type->code != v->type->code) grb_throw(GrB_DOMAIN_MISMATCH, "isequal: types differ (compare through eWiseMult(eq))");
+    if (u->nrows != v->nrows) { *result = false; return GrB_SUCCESS; }
+    const int64_t n = u->nrows;
+    if (n == 0 || u == v) { *result = true; return GrB_SUCCESS; }
+    int *differ = (int *)(g.d_scratch + 56);
+    dzero(differ, sizeof(int));
+    const int blocks = (int)(cdiv(n, 256) < 148 * 8 ? cdiv(n, 256) : 148 * 8);
+    GRB_TYPE_SWITCH(u->type->code, T,
+        GRB_LAUNCH("vec_isequal", k_vec_isequal<T>, blocks, 256, 0, (const T *)u->vals, u->present, (const T *)v->vals, v->present, n, differ));
+    int h = 0;
+    d2h(&h, differ, sizeof(int));
+    stream_sync();
+    *result = (h == 0);
+    API_END(u_)
+}

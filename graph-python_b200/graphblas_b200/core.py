@@ -583,7 +583,15 @@ class Vector(BaseType):
             raise TypeError(f"Expected Vector; got {type(other).__name__}")
         if check_dtype and self.dtype is not other.dtype:
             return False
-        if self._size != other._size or self.nvals != other.nvals:
+        if self._size != other._size:
+            return False
+        if self.dtype is other.dtype:
+            # one fused device pass + one read-back (GxB_b200_Vector_isequal) instead of the reference's sequence below
+            # (nvals, nvals, eWiseMult(eq), nvals, reduce(land): four host synchronisations per call); same answer
+            res = ffi.new("bool*")
+            call("GxB_b200_Vector_isequal", [_Handle(res), self, other])
+            return bool(res[0])
+        if self.nvals != other.nvals:
             return False
         if self.nvals == 0:
             return True

@@ -198,3 +198,33 @@ def test_option_getters(gb):
     assert lib.GxB_Matrix_Option_get_INT32(A._carg, lib.GxB_SPARSITY_STATUS, v) == lib.GrB_SUCCESS and v[0] == lib.GxB_SPARSE
     u = gb.Vector.from_coo([0], [1.0], size=3)
     assert lib.GxB_Vector_Option_get_INT32(u._carg, lib.GxB_SPARSITY_STATUS, v) == lib.GrB_SUCCESS and v[0] == lib.GxB_BITMAP
+
+
+def test_fused_isequal_matches_reference_semantics(gb):
+    """GxB_b200_Vector_isequal (one pass, one read-back) against what the reference's sequence eWiseMult(eq) + nvals +
+    reduce(land) decides: same pattern and `eq` on every common entry (so -0.0 == +0.0 and NaN != NaN)."""
+    from graphblas_b200 import Vector
+
+    n = 100003
+    rng = np.random.default_rng(3)
+    vals = rng.integers(-5, 5, size=n).astype(np.int64)
+    pres = rng.random(n) < 0.4
+    a = Vector.from_dense(vals, present=pres)
+    assert a.isequal(a.dup())
+    v2 = vals.copy(); k = int(np.flatnonzero(pres)[-1]); v2[k] += 1
+    assert not a.isequal(Vector.from_dense(v2, present=pres))          # one value differs (last present entry)
+    v3 = vals.copy(); k0 = int(np.flatnonzero(~pres)[0]); v3[k0] += 7
+    assert a.isequal(Vector.from_dense(v3, present=pres))              # a value under an absent entry does not count
+    p4 = pres.copy(); p4[k0] = True
+    assert not a.isequal(Vector.from_dense(vals, present=p4))          # pattern differs, values equal
+    assert not a.isequal(Vector.from_dense(vals[:-1], present=pres[:-1]))
+    f = Vector.from_dense(np.array([0.0, 1.5, np.nan]), present=np.array([True, True, False]))
+    g = Vector.from_dense(np.array([-0.0, 1.5, 3.0]), present=np.array([True, True, False]))
+    assert f.isequal(g)
+    h = Vector.from_dense(np.array([0.0, np.nan, 0.0]), present=np.array([True, True, False]))
+    assert not h.isequal(h.dup())                                      # NaN != NaN under eq, as in the reference
+    # different dtypes: the reference-shaped path (eWiseMult(eq) with type promotion)
+    i32 = Vector.from_dense(vals.astype(np.int32), present=pres)
+    assert a.isequal(i32) and not a.isequal(i32, check_dtype=True)
+    e1, e2 = Vector("FP32", 10), Vector("FP32", 10)
+    assert e1.isequal(e2)

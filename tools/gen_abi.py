@@ -328,6 +328,7 @@ GrB_Info GxB_b200_kernel_time_dump(void);
 GrB_Info GxB_b200_set_option(const char *name, int64_t value);
 GrB_Info GxB_b200_Vector_device_ptrs(void **values, void **present, const GrB_Vector v);
 GrB_Info GxB_b200_Vector_set_dense_nvals(GrB_Vector v, int64_t nvals);
+GrB_Info GxB_b200_Vector_isequal(bool *result, const GrB_Vector u, const GrB_Vector v);
 GrB_Info GxB_b200_Matrix_device_ptrs(void **rowptr, void **colidx, void **values, const GrB_Matrix A);
 GrB_Info GxB_b200_Matrix_prepare(GrB_Matrix A, int want_transpose);
 GrB_Info GxB_b200_Matrix_rmat(GrB_Matrix *A, GrB_Type type, int scale, int edgefactor, uint64_t seed,
