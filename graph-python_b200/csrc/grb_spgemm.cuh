@@ -642,7 +642,7 @@ constexpr int DOT_THREADS = 256;
 constexpr int DOT_SERIAL_MAX = 32;   // a thread handles the pair alone if the shorter row has <= this many entries
 
 template <class SR>
-__global__ void __launch_bounds__(DOT_THREADS, 6) k_dot_masked(DotArgs<typename SR::type> a) {
+__global__ void __launch_bounds__(DOT_THREADS, 8) k_dot_masked(DotArgs<typename SR::type> a) {
     using T = typename SR::type;
     using Mon = typename SR::Mon;
     __shared__ int q_e[DOT_THREADS];
