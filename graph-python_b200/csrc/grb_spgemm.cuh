@@ -255,9 +255,12 @@ __device__ __forceinline__ void panel_products(const int64_t *Ap, const uint32_t
                 const int l = __ffs(m) - 1; m &= m - 1;
                 const int wL = __shfl_sync(0xffffffffu, L, l), wc = __shfl_sync(0xffffffffu, c0, l);
                 const int64_t es = sq->s0[e0 + l], ep = pb + sq->poff[e0 + l];
-                for (int c = wc; c * 32 < wL; c += nwarps) {
-                    const int q = c * 32 + lane;
-                    if (q < wL) put(ld(ep, es + q));
+                for (int c = wc; c * 32 < wL; c += nwarps * PANEL_UNROLL) {
+                    Prod r[PANEL_UNROLL];                  // PANEL_UNROLL of this warp's chunks in flight before the inserts
+#pragma unroll
+                    for (int u = 0; u < PANEL_UNROLL; u++) { const int q = (c + u * nwarps) * 32 + lane; if (q < wL) r[u] = ld(ep, es + q); }
+#pragma unroll
+                    for (int u = 0; u < PANEL_UNROLL; u++) { const int q = (c + u * nwarps) * 32 + lane; if (q < wL) put(r[u]); }
                 }
             }
         }
