@@ -109,6 +109,30 @@ def test_spgemm_heavy_rows_hash_ranges(gb, panels):
         gb.set_option("spgemm_panels", 1)
 
 
+def test_spgemm_clustered_columns_ordered_emission(gb):
+    """Output rows whose columns sit in three narrow clusters (at 0, 100 K and 1.4 M): the order-preserving buckets of the
+    sort-free emission then hold hundreds of entries each (ranked by counting inside the bucket) -- rows must still come
+    out sorted and exact, in the hash-row kernel (~7 K entries per row) and in the heavy-row kernel (~10 K entries, the
+    first two clusters sharing one hash range)."""
+    rng = np.random.default_rng(13)
+    n = 1_500_000
+    for a_per_row, width in ((40, 4000), (80, 6000)):
+        m = 6
+        ar = np.repeat(np.arange(m), a_per_row)
+        ac = np.concatenate([rng.choice(2000, size=a_per_row, replace=False) for _ in range(m)])   # among the first 2000 rows of B
+        A = O.Mat.from_coo(ar, ac, rng.integers(1, 9, size=ar.size).astype(np.int64), m, n, "INT64")
+        br = np.repeat(np.arange(2000), 200)
+        lo = np.array([0, 100_000, 1_400_000])[rng.integers(0, 3, size=br.size)]
+        bc = lo + rng.integers(0, width, size=br.size)
+        keys = np.unique(br.astype(np.int64) * n + bc)
+        br, bc = keys // n, keys % n
+        B = O.Mat.from_coo(br, bc, rng.integers(1, 9, size=br.size).astype(np.int64), n, n, "INT64")
+        T = O.spgemm(A, B, "PLUS", "TIMES", "INT64")
+        gC = to_gpu_matrix(gb, A).mxm(to_gpu_matrix(gb, B), _sr("PLUS", "TIMES")).new()
+        assert gC.nvals == T.nnz
+        assert mat_equal(gC, T), (a_per_row, gb.last_kernel())
+
+
 def test_spgemm_rmat_scale14_fp64(gb):
     """BASELINE config 5a in small: A.mxm(A, plus_times) FP64 on a directed R-MAT graph, where > 80 % of the
     products sit in heavy rows (hash ranges and dense base panels); pattern exact, values within 1e-5."""
