@@ -176,6 +176,25 @@ class Expression:
     def dtype(self):
         return self.op.return_type if self.op is not None else self.args[0].dtype
 
+    # shape of the result, as the reference's expression objects expose it (core/expr.py; tests/test_infix.py:96-106)
+    @property
+    def size(self):
+        if self.out_cls is not Vector:
+            raise AttributeError(f"{self.out_cls.__name__} expression has no attribute 'size'")
+        return self.shape[0]
+
+    @property
+    def nrows(self):
+        if self.out_cls is not Matrix:
+            raise AttributeError(f"{self.out_cls.__name__} expression has no attribute 'nrows'")
+        return self.shape[0]
+
+    @property
+    def ncols(self):
+        if self.out_cls is not Matrix:
+            raise AttributeError(f"{self.out_cls.__name__} expression has no attribute 'ncols'")
+        return self.shape[1]
+
     def _new_output(self, dtype):
         dt = lookup_dtype(dtype) if dtype is not None else self.dtype
         if self.out_cls is Vector:

@@ -1,6 +1,7 @@
 """GPU: the reference's own golden vectors (tests/golden/reference_kats.json, transcribed from
 graphblas/tests/test_matrix.py:307-392 and test_vector.py:297-366, 1479-1491) through the reference-shaped
-API and the C-ABI of libgrb_b200.so.  Bit-exact (INT64)."""
+API and the C-ABI of libgrb_b200.so, plus the reference's infix (`@`) and outer-product tests
+(tests/test_infix.py:80-106, tests/test_vector.py:1520-1530) with their own fixtures.  Bit-exact (INT64)."""
 import numpy as np
 import pytest
 
@@ -117,3 +118,52 @@ def test_mask_must_be_marked(gb):
     A, v = _mat(gb, "A"), _vec(gb, "v")
     with pytest.raises(TypeError, match="Mask must be"):
         v.vxm(A).new(mask=v)
+
+
+def test_matmul_infix_as_in_reference(gb):
+    """graphblas/tests/test_infix.py:80-106 (test_matmul) with its own fixtures (:11-29): `left @ right` is the method
+    call with the default plus_times semiring, re-typable with `semiring.plus_times(left @ right)` and
+    `semiring.plus_times[float](...)`, for vxm / mxv / mxm (plain and transposed operands) and inner."""
+    from graphblas_b200 import Matrix, Vector, semiring
+
+    v1 = Vector.from_coo([0, 2], [2.0, 5.0])
+    v2 = Vector.from_coo([1, 2], [3.0, 7.0])
+    A1 = Matrix.from_coo([0, 0], [0, 1], [0.0, 4.0], ncols=3)
+    A2 = Matrix.from_coo([0, 2], [0, 0], [6.0, 8.0])
+    for method, left, right in [("vxm", v2, A2), ("vxm", v2, A1.T), ("mxv", A1, v1), ("mxv", A2.T, v1), ("mxm", A1, A2),
+                                ("mxm", A1.T, A2.T), ("mxm", A1, A1.T), ("mxm", A2.T, A2), ("inner", v1, v2),
+                                ("inner", v1, v1)]:
+        expected = getattr(left, method)(right, semiring.plus_times).new()
+        assert expected.isequal(semiring.plus_times(left @ right).new()), method
+        assert expected.isequal(semiring.plus_times[float](left @ right).new()), method
+        assert expected.isequal((left @ right).new()), method
+        if isinstance(left, Vector):
+            if not isinstance(right, Vector):
+                assert (left @ right).size == right.ncols
+        elif isinstance(right, Vector):
+            assert (left @ right).size == left.nrows
+        else:
+            assert (left @ right).nrows == left.nrows and (left @ right).ncols == right.ncols
+    # the values the reference's fixtures give (worked by hand): v2 @ A2 = [7*8] at 0; A1 @ v1 = [0*2] at 0 (explicit zero)
+    i, x = (v2 @ A2).new().to_coo()
+    assert list(i) == [0] and list(x) == [56.0]
+    i, x = (A1 @ v1).new().to_coo()
+    assert list(i) == [0] and list(x) == [0.0]
+    assert (v1 @ v2).new().value == 35.0 and (v1 @ v1).new().value == 29.0
+
+
+def test_outer_as_in_reference(gb):
+    """graphblas/tests/test_vector.py:1520-1530 (test_outer): v.outer(v) equals the column-by-row mxm, with the default
+    `times` and with `monoid.times`; golden values from the fixture v = {1: 1, 3: 1, 4: 2, 6: 0} (test_vector.py:33-37)."""
+    from graphblas_b200 import Matrix, Vector, monoid
+
+    v = Vector.from_coo([1, 3, 4, 6], [1, 1, 2, 0], dtype="INT64", size=7)
+    R = Matrix.from_coo([0] * 4, [1, 3, 4, 6], [1, 1, 2, 0], dtype="INT64", nrows=1, ncols=7)
+    C = Matrix.from_coo([1, 3, 4, 6], [0] * 4, [1, 1, 2, 0], dtype="INT64", nrows=7, ncols=1)
+    expected = C.mxm(R).new()
+    assert v.outer(v).new().isequal(expected)
+    assert v.outer(v, monoid.times).new().isequal(expected)
+    r, c, x = expected.to_coo()
+    assert expected.nvals == 16                                     # 4 x 4 entries, explicit zeros kept
+    want = {(i, j): a * b for i, a in zip([1, 3, 4, 6], [1, 1, 2, 0]) for j, b in zip([1, 3, 4, 6], [1, 1, 2, 0])}
+    assert {(int(i), int(j)): int(t) for i, j, t in zip(r, c, x)} == want
