@@ -167,3 +167,43 @@ def test_outer_as_in_reference(gb):
     assert expected.nvals == 16                                     # 4 x 4 entries, explicit zeros kept
     want = {(i, j): a * b for i, a in zip([1, 3, 4, 6], [1, 1, 2, 0]) for j, b in zip([1, 3, 4, 6], [1, 1, 2, 0])}
     assert {(int(i), int(j)): int(t) for i, j, t in zip(r, c, x)} == want
+
+
+def test_power_as_in_reference(gb):
+    """graphblas/tests/test_matrix.py:4367-4395 (test_power) on its fixture A (:33-41): A.power(i) for i < 50 against the
+    chain `expected << A @ expected` (the 49 plus_times products overflow INT64: both sides must wrap alike), the
+    transposed operand, min_plus, and the exceptional arguments.  The last link of the chain is also compared with the
+    C oracle's chain, bit for bit."""
+    from graphblas_b200 import semiring
+    from oracle import oracle as O
+
+    A = _mat(gb, "A")
+    expected = A.dup()
+    for i in range(1, 50):
+        assert A.power(i).new().isequal(expected), i
+        expected << A @ expected
+    x = resolve(FX, "A")
+    OA = O.Mat.from_coo(x["rows"], x["cols"], np.asarray(x["vals"], dtype=np.int64), 7, 7, "INT64")
+    E = OA
+    for _ in range(49):
+        E = O.spgemm(OA, E, "PLUS", "TIMES", "INT64")
+    r, c, v = expected.to_coo()
+    er, ec, ev = E.to_coo()
+    assert np.array_equal(r.astype(np.int64), er) and np.array_equal(c.astype(np.int64), ec) and np.array_equal(v, ev)
+    expected = A.T.new()
+    for i in range(1, 10):
+        assert A.T.power(i).new().isequal(expected), i
+        expected << A.T @ expected
+    expected = A.dup()
+    for i in range(1, 10):
+        assert A.power(i, semiring.min_plus).new().isequal(expected), i
+        expected << semiring.min_plus(A @ expected)
+    with pytest.raises(TypeError, match="must be a positive integer"):
+        A.power(1.5)
+    with pytest.raises(ValueError, match="must be a positive integer"):
+        A.power(-1)
+    with pytest.raises(ValueError, match="must be a positive integer"):
+        A.power(0)
+    B = gb.Matrix("INT64", 2, 3)
+    with pytest.raises(gb.DimensionMismatch):
+        B.power(2)
