@@ -28,7 +28,9 @@
 enum TypeCode { TC_BOOL = 0, TC_INT8, TC_INT16, TC_INT32, TC_INT64, TC_UINT8, TC_UINT16, TC_UINT32,
                 TC_UINT64, TC_FP32, TC_FP64, TC_COUNT };
 enum OpCode { OP_FIRST = 0, OP_SECOND, OP_ONEB, OP_ANY, OP_PLUS, OP_MINUS, OP_TIMES, OP_DIV, OP_MIN, OP_MAX,
-              OP_LOR, OP_LAND, OP_LXOR, OP_LXNOR, OP_EQ, OP_NE, OP_GT, OP_LT, OP_GE, OP_LE, OP_COUNT };
+              OP_LOR, OP_LAND, OP_LXOR, OP_LXNOR, OP_EQ, OP_NE, OP_GT, OP_LT, OP_GE, OP_LE,
+              OP_RDIV,   // internal: div with the operands swapped (vxm hands the kernels u as the SECOND operand)
+              OP_COUNT };
 enum IdxOp { IDX_TRIL = 0, IDX_TRIU, IDX_DIAG, IDX_OFFDIAG };
 enum ObjKind { K_SCALAR = 0, K_VECTOR = 1, K_MATRIX = 2 };
 

@@ -377,7 +377,9 @@ static void vector_product(GB_Object *w, GB_Object *mask, const GrB_BinaryOp acc
     }
     const int tcode = sr->tcode, mon = sr->mon;
     int mul = sr->mul;
-    if (is_vxm) mul = (mul == OP_FIRST) ? OP_SECOND : (mul == OP_SECOND) ? OP_FIRST : mul;
+    // the kernels multiply (matrix entry, vector entry); vxm's multiply is (vector entry, matrix entry): swap the
+    // operand-selecting and the non-commutative multiplies
+    if (is_vxm) mul = (mul == OP_FIRST) ? OP_SECOND : (mul == OP_SECOND) ? OP_FIRST : (mul == OP_DIV) ? OP_RDIV : mul;
     // pull reads rows of (is_vxm != tran) ? A' : A
     const bool use_transpose = (is_vxm != tran);
     // reconcile operand types with the semiring's type (cast copies; the common case needs none)

@@ -70,6 +70,7 @@ template <class T> struct BinOp<OP_PLUS, T> { static HD T apply(T x, T y) { retu
 template <class T> struct BinOp<OP_MINUS, T> { static HD T apply(T x, T y) { return op_minus(x, y); } };
 template <class T> struct BinOp<OP_TIMES, T> { static HD T apply(T x, T y) { return op_times(x, y); } };
 template <class T> struct BinOp<OP_DIV, T> { static HD T apply(T x, T y) { return op_div(x, y); } };
+template <class T> struct BinOp<OP_RDIV, T> { static HD T apply(T x, T y) { return op_div(y, x); } };
 template <class T> struct BinOp<OP_MIN, T> { static HD T apply(T x, T y) { return op_min(x, y); } };
 template <class T> struct BinOp<OP_MAX, T> { static HD T apply(T x, T y) { return op_max(x, y); } };
 template <class T> struct BinOp<OP_LOR, T> { static HD T apply(T x, T y) { return (T)((x != (T)0) || (y != (T)0)); } };
@@ -88,6 +89,7 @@ template <class T> HD T binop_rt(int op, T x, T y) {
     case OP_MINUS: return op_minus(x, y);
     case OP_TIMES: return op_times(x, y);
     case OP_DIV: return op_div(x, y);
+    case OP_RDIV: return op_div(y, x);
     case OP_MIN: return op_min(x, y);
     case OP_MAX: return op_max(x, y);
     case OP_LOR: return (T)((x != (T)0) || (y != (T)0));

@@ -195,6 +195,23 @@ def _initialize():
                 td._typed[t] = div._typed[t]
 
 
+    # Division semirings as the reference names them (graphblas/core/operator/semiring.py: `plus_div` is hidden; `plus_cdiv`
+    # is C division on the integer types, `plus_truediv` divides in floating point -- integer operands are cast to FP64
+    # by the library, the result is FP64; tests/test_op.py:950-965)
+    pdiv = getattr(semiring, "plus_div", None)
+    if pdiv is not None:
+        cdiv_, tdiv = _get(semiring, Semiring, "plus_cdiv"), _get(semiring, Semiring, "plus_truediv")
+        for t, typed in pdiv._typed.items():
+            if t.startswith("FP"):
+                tdiv._typed[t] = typed
+            else:
+                cdiv_._typed[t] = typed
+        if "FP64" in pdiv._typed:
+            for t in ("INT8", "INT16", "INT32", "INT64", "UINT8", "UINT16", "UINT32", "UINT64", "BOOL"):
+                tdiv._typed.setdefault(t, pdiv._typed["FP64"])
+        delattr(semiring, "plus_div")
+
+
 _initialize()
 
 _STRING_BINARY = {"+": "plus", "-": "minus", "*": "times", "/": "div", "min": "min", "max": "max",

@@ -207,3 +207,28 @@ def test_power_as_in_reference(gb):
     B = gb.Matrix("INT64", 2, 3)
     with pytest.raises(gb.DimensionMismatch):
         B.power(2)
+
+
+def test_div_semirings_as_in_reference(gb):
+    """graphblas/tests/test_op.py:950-965 (test_div_semirings): plus_div is not exposed; plus_cdiv is C division on INT64
+    ((-1)/2 + (-3)/2 = 0 + -1), plus_truediv divides in FP64 (-0.5 + -1.5) and returns FP64."""
+    from graphblas_b200 import Matrix, dtypes, semiring
+
+    assert not hasattr(semiring, "plus_div")
+    A1 = Matrix.from_coo([0, 1], [0, 0], [-1, -3])
+    A2 = Matrix.from_coo([0, 1], [0, 0], [2, 2])
+    result = A1.T.mxm(A2, semiring.plus_cdiv).new()
+    assert result[0, 0].new() == -1
+    assert result.dtype == dtypes.INT64
+    result = A1.T.mxm(A2, semiring.plus_truediv).new()
+    assert result[0, 0].new() == -2
+    assert result.dtype == dtypes.FP64
+    # the same through the vector products (operand order matters for a non-commutative multiply)
+    from graphblas_b200 import Vector
+
+    u = Vector.from_coo([0, 1], [12, 20])
+    B = Matrix.from_coo([0, 1], [0, 0], [5, 3])
+    i, x = u.vxm(B, semiring.plus_cdiv).new().to_coo()       # u(0)/B(0,0) + u(1)/B(1,0) = 2 + 6
+    assert list(i) == [0] and list(x) == [8]
+    i, x = B.T.mxv(u, semiring.plus_cdiv).new().to_coo()     # B(0,0)/u(0) + B(1,0)/u(1) = 0 + 0
+    assert list(i) == [0] and list(x) == [0]

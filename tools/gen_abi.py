@@ -55,7 +55,7 @@ GRB_SEMIRINGS = {
 }
 SEMIRINGS_NUM = [
     ("PLUS", "TIMES"), ("PLUS", "PLUS"), ("PLUS", "FIRST"), ("PLUS", "SECOND"), ("PLUS", "PAIR"),
-    ("PLUS", "MIN"), ("PLUS", "MAX"),
+    ("PLUS", "MIN"), ("PLUS", "MAX"), ("PLUS", "DIV"),
     ("MIN", "PLUS"), ("MIN", "TIMES"), ("MIN", "FIRST"), ("MIN", "SECOND"), ("MIN", "MAX"),
     ("MAX", "PLUS"), ("MAX", "TIMES"), ("MAX", "FIRST"), ("MAX", "SECOND"), ("MAX", "MIN"),
     ("ANY", "PAIR"), ("ANY", "FIRST"), ("ANY", "SECOND"), ("ANY", "TIMES"), ("ANY", "PLUS"),
