@@ -54,6 +54,14 @@ void orc_free(void *p) { free(p); }
         case OP_PLUS: return (T)((U)x + (U)y);                                        \
         case OP_MINUS: return (T)((U)x - (U)y);                                       \
         case OP_TIMES: return (T)((U)x * (U)y);                                       \
+        case OP_DIV: { /* SuiteSparse integer division (GB_IDIV_SIGNED / GB_IDIV_UNSIGNED): never traps; */ \
+            /* x/0 = 0, type max or type min by the sign of x; x/-1 = -x computed unsigned */                    \
+            const int is_signed = ((T)-1 < (T)0);                                     \
+            const T tmax = (T)(((U)~(U)0) >> (is_signed ? 1 : 0));                    \
+            const T tmin = is_signed ? (T)(~tmax) : (T)0;                             \
+            if (y == 0) return x == 0 ? (T)0 : (x < (T)0 ? tmin : tmax);              \
+            if (is_signed && y == (T)-1) return (T)((U)0 - (U)x);                     \
+            return (T)(x / y); }                                                      \
         case OP_MIN: return x < y ? x : y;                                            \
         case OP_MAX: return x > y ? x : y;                                            \
         case OP_LOR: return (T)((x != 0) || (y != 0));                                \

@@ -157,3 +157,27 @@ def test_rmat_generator_is_deterministic_and_skewed():
     deg = np.bincount(r1, minlength=1 << 12)
     assert deg.max() > 20 * max(1, int(np.median(deg)))  # heavy tail
     assert r1.size > 0.7 * (16 << 12)
+
+
+def test_div_semirings_reference_values():
+    """reference tests/test_op.py:950-965: A1' (+).(/) A2 with A1 = [-1, -3]', A2 = [2, 2]' is -1 under C division on INT64
+    and -2 in FP64; plus the operand order of vxm / mxv and the integer-division corner cases SuiteSparse defines
+    (x / 0 saturates by the sign of x, 0 / 0 = 0, INT64_MIN / -1 wraps)."""
+    A1 = O.Mat.from_coo([0, 1], [0, 0], np.array([-1, -3], dtype=np.int64), 2, 1, "INT64")
+    A2 = O.Mat.from_coo([0, 1], [0, 0], np.array([2, 2], dtype=np.int64), 2, 1, "INT64")
+    assert O.spgemm(A1.transpose(), A2, "PLUS", "DIV", "INT64").values.tolist() == [-1]
+    F1 = O.Mat.from_coo([0, 1], [0, 0], np.array([-1.0, -3.0]), 2, 1, "FP64")
+    F2 = O.Mat.from_coo([0, 1], [0, 0], np.array([2.0, 2.0]), 2, 1, "FP64")
+    assert O.spgemm(F1.transpose(), F2, "PLUS", "DIV", "FP64").values.tolist() == [-2.0]
+    u = O.Vec.from_coo([0, 1], [12, 20], 2, "INT64")
+    B = O.Mat.from_coo([0, 1], [0, 0], np.array([5, 3], dtype=np.int64), 2, 1, "INT64")
+    w = O.Vec.from_coo([], [], 1, "INT64")
+    O.vxm(w, u, B, "PLUS", "DIV", "INT64")                     # u(i) / B(i,0): 2 + 6
+    assert w.to_coo()[1].tolist() == [8]
+    w = O.Vec.from_coo([], [], 1, "INT64")
+    O.mxv(w, B, u, "PLUS", "DIV", "INT64", tran0=True)         # B(i,0) / u(i): 0 + 0
+    assert w.to_coo()[1].tolist() == [0]
+    imin, imax = np.iinfo(np.int64).min, np.iinfo(np.int64).max
+    X = O.Mat.from_coo([0, 1, 2, 3], [0, 1, 2, 3], np.array([7, -7, 0, imin], dtype=np.int64), 4, 4, "INT64")
+    Y = O.Mat.from_coo([0, 1, 2, 3], [0, 1, 2, 3], np.array([0, 0, 0, -1], dtype=np.int64), 4, 4, "INT64")
+    assert O.spgemm(X, Y, "PLUS", "DIV", "INT64").values.tolist() == [imax, imin, 0, imin]
