@@ -435,7 +435,9 @@ static void matrix_set_element_impl(GB_Object *C, T x, int xcode, uint64_t i, ui
     int64_t pos = csr_find(C->csr, (int64_t)i, (int64_t)j);
     if (pos >= 0) {
         d2d((char *)C->csr.vals + pos * ts, dxc, ts);
-        if (C->csc_valid) { csr_free(C->csc); C->csc_valid = false; }
+        // an in-place edit: every cache that holds a copy of the values (transpose, typed copy of the values,
+        // column panels, stream form) is stale now
+        obj_invalidate_caches(C);
     } else {
         int64_t nnz = C->csr.nnz;
         uint64_t *keys = dalloc<uint64_t>(nnz + 1);
@@ -684,6 +686,7 @@ GrB_Info GxB_b200_Vector_import_dense(GrB_Vector v_, const void *values, const i
         CUDA_TRY(cudaMemsetAsync(v->present, 1, (size_t)n, g.stream));
         v->nvals = (int64_t)n; v->nvals_known = true; v->list_valid = false;
     }
+    stream_sync();     // the caller may reuse or free its (possibly pinned) buffers as soon as this returns
     API_END(v_)
 }
 GrB_Info GxB_b200_Vector_export_dense(void *values, int8_t *present, GrB_Index n, const GrB_Vector v_) {

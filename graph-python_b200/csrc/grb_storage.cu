@@ -174,7 +174,8 @@ void csr_drop_caches(Csr &c) {
     for (int p = 0; p < c.n_panels; p++) csr_free(c.panels[p]);
     delete[] c.panels; c.panels = nullptr; c.n_panels = 0; c.panel_code = -1; c.panel_width = 0;
 }
-// Matrices are replaced, never edited in place (mat_set_csr), so a typed copy of the values stays valid for the
+// Matrices are replaced (mat_set_csr) or, for GrB_Matrix_setElement on an existing entry, edited in place followed by
+// obj_invalidate_caches, so a typed copy of the values stays valid for the
 // life of the Csr: BOOL adjacency x INT32 vector products cast once, not per call.
 const void *csr_vals_as(Csr &c, int from_code, int to_code) {
     if (from_code == to_code) return c.vals;
