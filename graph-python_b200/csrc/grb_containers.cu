@@ -88,7 +88,7 @@ void mat_ensure_csc(GB_Object *o) {
     o->csc_valid = true;
 }
 
-static GB_Object *obj_new(int kind, GrB_Type type, uint64_t nrows, uint64_t ncols) {
+GB_Object *obj_new(int kind, GrB_Type type, uint64_t nrows, uint64_t ncols) {
     require_init();
     if (!type) grb_throw(GrB_NULL_POINTER, "type is NULL");
     if (nrows >= (1ull << 32) || ncols >= (1ull << 32))
@@ -104,7 +104,7 @@ static GB_Object *obj_new(int kind, GrB_Type type, uint64_t nrows, uint64_t ncol
     } catch (...) { delete o; throw; }
     return o;
 }
-static void obj_free(GB_Object *o) {
+void obj_free(GB_Object *o) {
     obj_release_storage(o);
     o->magic = GRB_FREED;
     delete o;
@@ -123,7 +123,7 @@ static GB_Object *obj_dup(GB_Object *a) {
     }
     return o;
 }
-static void obj_clear(GB_Object *o) {
+void obj_clear(GB_Object *o) {
     if (o->kind == K_MATRIX) {
         Csr c; csr_empty(c, o->nrows, o->ncols, o->type->size);
         mat_set_csr(o, c);
@@ -267,7 +267,8 @@ __global__ void k_make_keys2(const uint64_t *I, const uint64_t *J, uint64_t nrow
 
 static int dup_code(const GrB_BinaryOp dup, GB_Object *o) {
     if (!dup) return -1;
-    if (dup->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be used as dup");
+    op_need_kernel(dup->op, dup->name);
+    if (op_is_cmp(dup->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be used as dup");
     (void)o;
     return dup->op;
 }
@@ -743,7 +744,7 @@ template <class T> __global__ void k_fill(T *p, int64_t n, const T *one) {
 // Ownership transfer as in reference graphblas/core/ss/matrix.py:1282-1352 (import_csr -> pack) and :744-1162
 // (export -> unpack): host buffers come from / go to the allocator given to GxB_init (numpy's, so that
 // claim_buffer/unclaim_buffer keep working).  HBM is the only place matrix data lives afterwards.
-static void pack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index Ap_size,
+void pack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index Ap_size,
                      GrB_Index Ai_size, GrB_Index Ax_size, bool iso) {
     if (A->kind != K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "pack needs a matrix");
     if (!Ap || !Ai || !Ax || !*Ap || !*Ax) grb_throw(GrB_NULL_POINTER, "Ap, Ai or Ax is NULL");
@@ -767,7 +768,7 @@ static void pack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, 
     if (*Ai) { g.h_free(*Ai); *Ai = nullptr; }
     g.h_free(*Ax); *Ax = nullptr;
 }
-static void unpack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index *Ap_size,
+void unpack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index *Ap_size,
                        GrB_Index *Ai_size, GrB_Index *Ax_size, bool *iso, bool *jumbled) {
     if (A->kind != K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "unpack needs a matrix");
     if (!Ap || !Ai || !Ax || !Ap_size || !Ai_size || !Ax_size) grb_throw(GrB_NULL_POINTER, "output pointers are NULL");

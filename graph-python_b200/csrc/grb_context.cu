@@ -113,9 +113,28 @@ GRB_MONOID_LIST(X)
 GRB_SEMIRING_LIST(X)
 #undef X
 
+// registry-only handles: distinct objects (the reference keys dictionaries by handle), all marked OP_UNSUPPORTED
+#define X(SYM) static GB_UnaryOp_opaque obj_##SYM = {OP_UNSUPPORTED, -1, #SYM}; GrB_UnaryOp SYM = &obj_##SYM;
+GRB_UNOP_STUB_LIST(X)
+#undef X
+#define X(SYM) static GB_BinaryOp_opaque obj_##SYM = {OP_UNSUPPORTED, -1, -1, #SYM}; GrB_BinaryOp SYM = &obj_##SYM;
+GRB_BINOP_STUB_LIST(X)
+#undef X
+#define X(SYM) static GB_IndexUnaryOp_opaque obj_##SYM = {OP_UNSUPPORTED, #SYM}; GrB_IndexUnaryOp SYM = &obj_##SYM;
+GRB_IDXOP_STUB_LIST(X)
+#undef X
+#define X(SYM) static GB_Monoid_opaque obj_##SYM = {OP_UNSUPPORTED, -1, #SYM}; GrB_Monoid SYM = &obj_##SYM;
+GRB_MONOID_STUB_LIST(X)
+#undef X
+#define X(SYM) static GB_Semiring_opaque obj_##SYM = {OP_UNSUPPORTED, OP_UNSUPPORTED, -1, #SYM}; GrB_Semiring SYM = &obj_##SYM;
+GRB_SEMIRING_STUB_LIST(X)
+#undef X
+
 static GB_IndexUnaryOp_opaque obj_TRIL = {IDX_TRIL, "GrB_TRIL"}, obj_TRIU = {IDX_TRIU, "GrB_TRIU"},
                               obj_DIAG = {IDX_DIAG, "GrB_DIAG"}, obj_OFFDIAG = {IDX_OFFDIAG, "GrB_OFFDIAG"};
 GrB_IndexUnaryOp GrB_TRIL = &obj_TRIL, GrB_TRIU = &obj_TRIU, GrB_DIAG = &obj_DIAG, GrB_OFFDIAG = &obj_OFFDIAG;
+
+extern "C" { double GxB_HYPER_DEFAULT = 0.0625, GxB_ALWAYS_HYPER = 1.0, GxB_NEVER_HYPER = -1.0; }   // no hypersparse format here
 
 static GB_Descriptor_opaque *make_desc(bool r, bool c, bool s, bool t0, bool t1) {
     GB_Descriptor_opaque *d = new GB_Descriptor_opaque();
@@ -245,16 +264,54 @@ GrB_Info GrB_Descriptor_error(const char **error, const GrB_Descriptor d) {
     return GrB_SUCCESS;
 }
 
-// user-defined semirings are refused: no JIT, no CPU fallback (north_star)
+// GrB_Semiring_new composes BUILT-IN monoids and multiplies (the reference's registry does this at import for plus_pow,
+// *_truediv, ... graphblas/core/operator/semiring.py:205-243, 370-390).  The handle always comes into being; whether it can
+// be used is decided at the call: a (monoid, multiply, type) triple with an instantiated kernel runs, anything else --
+// registry-only operators, comparison multiplies, and every user-defined function (there is no JIT and no CPU fallback,
+// north_star) -- returns GrB_NOT_IMPLEMENTED from GrB_mxm / GrB_mxv / GrB_vxm.
 GrB_Info GrB_Semiring_new(GrB_Semiring *semiring, GrB_Monoid add, GrB_BinaryOp multiply) {
-    (void)add; (void)multiply;
-    if (semiring) *semiring = nullptr;
-    return GrB_NOT_IMPLEMENTED;
-}
-GrB_Info GrB_Semiring_free(GrB_Semiring *semiring) {
-    if (semiring) *semiring = nullptr;  // built-ins are static; nothing to release
+    if (!semiring) return GrB_NULL_POINTER;
+    *semiring = nullptr;
+    if (!add || !multiply) return GrB_NULL_POINTER;
+    GB_Semiring_opaque *s = new GB_Semiring_opaque{add->op, multiply->op, add->tcode, "user semiring", true};
+    const bool usable = add->op != OP_UNSUPPORTED && multiply->op != OP_UNSUPPORTED && !op_is_cmp(multiply->op) &&
+                        multiply->xcode == add->tcode && multiply->zcode == add->tcode;
+    if (!usable) { s->mon = OP_UNSUPPORTED; s->mul = OP_UNSUPPORTED; }
+    *semiring = s;
     return GrB_SUCCESS;
 }
+GrB_Info GrB_Semiring_free(GrB_Semiring *semiring) {
+    if (semiring && *semiring && (*semiring)->heap) delete *semiring;     // built-ins are static
+    if (semiring) *semiring = nullptr;
+    return GrB_SUCCESS;
+}
+// user-defined operators need a JIT or a CPU: refused (the symbols exist because the reference looks them up by name)
+GrB_Info GrB_UnaryOp_new(GrB_UnaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype) {
+    (void)function; (void)ztype; (void)xtype;
+    if (op) *op = nullptr;
+    return GrB_NOT_IMPLEMENTED;
+}
+GrB_Info GrB_BinaryOp_new(GrB_BinaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype, GrB_Type ytype) {
+    (void)function; (void)ztype; (void)xtype; (void)ytype;
+    if (op) *op = nullptr;
+    return GrB_NOT_IMPLEMENTED;
+}
+GrB_Info GrB_IndexUnaryOp_new(GrB_IndexUnaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype, GrB_Type ytype) {
+    (void)function; (void)ztype; (void)xtype; (void)ytype;
+    if (op) *op = nullptr;
+    return GrB_NOT_IMPLEMENTED;
+}
+GrB_Info GrB_UnaryOp_free(GrB_UnaryOp *op) { if (op) *op = nullptr; return GrB_SUCCESS; }
+GrB_Info GrB_BinaryOp_free(GrB_BinaryOp *op) { if (op) *op = nullptr; return GrB_SUCCESS; }
+GrB_Info GrB_IndexUnaryOp_free(GrB_IndexUnaryOp *op) { if (op) *op = nullptr; return GrB_SUCCESS; }
+GrB_Info GrB_Monoid_free(GrB_Monoid *op) { if (op) *op = nullptr; return GrB_SUCCESS; }
+// operator handles carry no error state: the string is always empty (graphblas/exceptions.py:143-154 reads it)
+GrB_Info GrB_Semiring_error(const char **error, const GrB_Semiring op) { (void)op; if (error) *error = ""; return GrB_SUCCESS; }
+GrB_Info GrB_Monoid_error(const char **error, const GrB_Monoid op) { (void)op; if (error) *error = ""; return GrB_SUCCESS; }
+GrB_Info GrB_BinaryOp_error(const char **error, const GrB_BinaryOp op) { (void)op; if (error) *error = ""; return GrB_SUCCESS; }
+GrB_Info GrB_UnaryOp_error(const char **error, const GrB_UnaryOp op) { (void)op; if (error) *error = ""; return GrB_SUCCESS; }
+GrB_Info GrB_IndexUnaryOp_error(const char **error, const GrB_IndexUnaryOp op) { (void)op; if (error) *error = ""; return GrB_SUCCESS; }
+GrB_Info GrB_Type_error(const char **error, const GrB_Type t) { (void)t; if (error) *error = ""; return GrB_SUCCESS; }
 
 // ---------------- B200 plumbing ----------------
 GrB_Info GxB_b200_set_stream(void *cuda_stream) {

@@ -27,7 +27,8 @@ static EpiArgs<T> epi_for(GB_Object *w, GB_Object *mask, const DescFlags &f, int
 
 static int accum_code(const GrB_BinaryOp accum) {
     if (!accum) return -1;
-    if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+    op_need_kernel(accum->op, accum->name);
+    if (op_is_cmp(accum->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
     return accum->op;
 }
 
@@ -237,7 +238,8 @@ static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_Binary
     DescFlags f = desc_flags(desc);
     int acc = accum_code(accum);
     int xcode = op->xcode, zcode = op->zcode;
-    const bool cmp = op->op >= OP_EQ;
+    op_need_kernel(op->op, op->name);
+    const bool cmp = op_is_cmp(op->op);
     void *uc = nullptr, *vc = nullptr;
     const void *uv = u->vals, *vv = v->vals;
     if (u->type->code != xcode) { uc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(u->vals, u->type->code, uc, xcode, n); uv = uc; }
@@ -315,7 +317,8 @@ static GrB_Info vector_apply2nd(GrB_Vector w_, const GrB_Vector mask_, const GrB
     DescFlags f = desc_flags(desc);
     int acc = accum_code(accum);
     int xcode = op->xcode, zcode = op->zcode;
-    const bool cmp = op->op >= OP_EQ;
+    op_need_kernel(op->op, op->name);
+    const bool cmp = op_is_cmp(op->op);
     void *uc = nullptr;
     const void *uv = u->vals;
     if (u->type->code != xcode) { uc = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[xcode]); cast_array(u->vals, u->type->code, uc, xcode, n); uv = uc; }
@@ -383,6 +386,7 @@ template <class T>
 static GrB_Info reduce_to_scalar(T *c, const GrB_BinaryOp accum, const GrB_Monoid monoid, GB_Object *A, int ccode) {
     if (!c) grb_throw(GrB_NULL_POINTER, "c is NULL");
     if (!monoid) grb_throw(GrB_NULL_POINTER, "monoid is NULL");
+    op_need_kernel(monoid->op, monoid->name);
     int mcode = monoid->tcode;
     const void *vals; const uint8_t *present; int64_t n; bool iso = false; int vcode = A->type->code;
     if (A->kind == K_MATRIX) { vals = A->csr.vals; present = nullptr; n = A->csr.nnz; iso = A->csr.iso; }
@@ -408,7 +412,8 @@ static GrB_Info reduce_to_scalar(T *c, const GrB_BinaryOp accum, const GrB_Monoi
         else if (mcode == TC_UINT64) r = (T)as_u64;
         else r = (T)as_i64;
         if (accum) {
-            if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+            op_need_kernel(accum->op, accum->name);
+    if (op_is_cmp(accum->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
             *c = binop_rt<T>(accum->op, *c, r);
         } else *c = r;
     } else if (!accum) {

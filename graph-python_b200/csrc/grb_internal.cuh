@@ -31,6 +31,27 @@ enum OpCode { OP_FIRST = 0, OP_SECOND, OP_ONEB, OP_ANY, OP_PLUS, OP_MINUS, OP_TI
               OP_LOR, OP_LAND, OP_LXOR, OP_LXNOR, OP_EQ, OP_NE, OP_GT, OP_LT, OP_GE, OP_LE,
               OP_RDIV,   // internal: div with the operands swapped (vxm hands the kernels u as the SECOND operand)
               OP_COUNT };
+// ---- semirings on INT8 / INT16 / UINT8 / UINT16 (reference graphblas/core/operator/semiring.py:170-204 registers them).
+// There are no 8/16-bit atomics, so they are computed in the 32-bit type of the same signedness and wrapped to the narrow
+// type afterwards.  That is exact when the monoid is PLUS (mod 2^32 then mod 2^8/2^16) or when the multiply cannot leave the
+// narrow range (first, second, pair, min, max); where it can and the monoid orders values (min_plus, min_times, max_plus,
+// max_times) or saturates (div), the multiply itself wraps: internal multiply code = op | narrow id << 8.
+enum NarrowId { NARROW_INT8 = 1, NARROW_INT16 = 2, NARROW_UINT8 = 3, NARROW_UINT16 = 4 };
+#define GRB_NARROW_OPS(OPNAME)                                                                    \
+    OP_##OPNAME##_N1 = OP_##OPNAME | (1 << 8), OP_##OPNAME##_N2 = OP_##OPNAME | (2 << 8),         \
+    OP_##OPNAME##_N3 = OP_##OPNAME | (3 << 8), OP_##OPNAME##_N4 = OP_##OPNAME | (4 << 8)
+enum NarrowOp { GRB_NARROW_OPS(PLUS), GRB_NARROW_OPS(TIMES), GRB_NARROW_OPS(DIV), GRB_NARROW_OPS(RDIV) };
+inline bool tc_is_narrow(int c) { return c == TC_INT8 || c == TC_INT16 || c == TC_UINT8 || c == TC_UINT16; }
+inline int tc_wide_of(int c) { return (c == TC_INT8 || c == TC_INT16) ? TC_INT32 : TC_UINT32; }
+inline int narrow_id_of(int c) { return c == TC_INT8 ? NARROW_INT8 : c == TC_INT16 ? NARROW_INT16 : c == TC_UINT8 ? NARROW_UINT8 : NARROW_UINT16; }
+inline int narrow_mul(int mon, int mul, int narrow_code) {
+    const bool ordered = (mon == OP_MIN || mon == OP_MAX) && (mul == OP_PLUS || mul == OP_TIMES);
+    return (ordered || mul == OP_DIV || mul == OP_RDIV) ? (mul | (narrow_id_of(narrow_code) << 8)) : mul;
+}
+
+// handles that exist for the reference's operator registry only (tools/gen_abi.py registry_only_*): no kernel
+#define OP_UNSUPPORTED 1000
+inline bool op_is_cmp(int op) { return op >= OP_EQ && op <= OP_LE; }
 enum IdxOp { IDX_TRIL = 0, IDX_TRIU, IDX_DIAG, IDX_OFFDIAG };
 enum ObjKind { K_SCALAR = 0, K_VECTOR = 1, K_MATRIX = 2 };
 
@@ -42,7 +63,7 @@ struct GB_UnaryOp_opaque { int op; int tcode; const char *name; };
 struct GB_IndexUnaryOp_opaque { int op; const char *name; };
 struct GB_BinaryOp_opaque { int op; int xcode; int zcode; const char *name; };
 struct GB_Monoid_opaque { int op; int tcode; const char *name; };
-struct GB_Semiring_opaque { int mon; int mul; int tcode; const char *name; };
+struct GB_Semiring_opaque { int mon; int mul; int tcode; const char *name; bool heap; };   // heap: made by GrB_Semiring_new
 
 #define GRB_MAGIC 0x42323030u   /* "B200" */
 #define GRB_FREED 0x46524545u
@@ -196,6 +217,14 @@ GB_Object *obj_check(const void *h, const char *what);   // NULL -> GrB_NULL_POI
 GB_Object *obj_check_lazy(const void *h, const char *what);   // same, but leaves a column-imported matrix as it is (hot paths pick a side)
 void mat_ensure_csr(GB_Object *o);                        // rows of A from the cached columns, if A was imported by columns
 void csr_free(Csr &c);
+GB_Object *obj_new(int kind, GrB_Type type, uint64_t nrows, uint64_t ncols);
+void obj_free(GB_Object *o);
+void obj_clear(GB_Object *o);
+// SuiteSparse-style hand-off with ownership transfer (grb_containers.cu; the import/export forms are in grb_exchange.cu)
+void pack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index Ap_size, GrB_Index Ai_size,
+              GrB_Index Ax_size, bool iso);
+void unpack_csx(GB_Object *A, bool by_col, GrB_Index **Ap, GrB_Index **Ai, void **Ax, GrB_Index *Ap_size, GrB_Index *Ai_size,
+                GrB_Index *Ax_size, bool *iso, bool *jumbled);
 void obj_release_storage(GB_Object *o);
 void obj_invalidate_caches(GB_Object *o);                 // after the CSR changed: drop csc + tiles
 void vec_alloc(GB_Object *o);                             // allocate dense storage (zeroed presence)
@@ -214,7 +243,7 @@ void csr_ensure_tiles(Csr &c, int tile_nnz);
 void csr_ensure_hubs(Csr &c, int capacity);               // build / rebuild the hub cache for at most `capacity` hubs
 void csr_ensure_panels(Csr &c, int npanels, const void *vals, int tcode);   // split by column ranges (values in tcode)
 void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)
-const void *csr_vals_as(Csr &c, int from_code, int to_code);   // c.vals, or a cached typed copy of them
+const void *csr_vals_as(Csr &c, int from_code, int to_code, int via_code = -1);   // c.vals, or a cached typed copy of them
 void mat_set_csr(GB_Object *o, Csr &c);                   // take ownership of c as o's CSR
 Csr csr_dup(const Csr &a, size_t tsize);
 Csr vec_as_csr_column(GB_Object *v);                      // n x 1 matrix view of a vector (copy)
@@ -259,4 +288,9 @@ inline void require_init() {
     default: grb_throw(GrB_INVALID_VALUE, "unknown type code");                    \
     }
 
+inline void op_need_kernel(int op, const char *name) {
+    if (op == OP_UNSUPPORTED)
+        grb_throw(GrB_NOT_IMPLEMENTED, std::string(name ? name : "operator") +
+                  " has no sm_100a kernel in libgrb_b200 (registry-only handle; there is no CPU fallback)");
+}
 inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -16,7 +16,8 @@ static inline int nblk(int64_t n, int b = 256) { return (int)cdiv(n > 0 ? n : 1,
 
 int accum_code_of(const GrB_BinaryOp accum) {
     if (!accum) return -1;
-    if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+    op_need_kernel(accum->op, accum->name);
+    if (op_is_cmp(accum->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
     return accum->op;
 }
 
@@ -206,7 +207,8 @@ static void matrix_ewise(GrB_Matrix C_, const GrB_Matrix M_, const GrB_BinaryOp 
         (mask && (obj_rows(mask) != va.nrows || obj_cols(mask) != va.ncols)))
         grb_throw(GrB_DIMENSION_MISMATCH, "eWise: matrix shapes differ");
     const int xcode = op->xcode, zcode = op->zcode;
-    const bool cmp = op->op >= OP_EQ;
+    op_need_kernel(op->op, op->name);
+    const bool cmp = op_is_cmp(op->op);
     Csr ac, bc; bool ac_on = false, bc_on = false;
     const Csr *pa = va.csr, *pb = vb.csr;
     if (A->type->code != xcode) { ac = csr_dup(*pa, A->type->size); csr_cast_values(ac, A->type->code, xcode); ac_on = true; pa = &ac; }
@@ -362,6 +364,7 @@ GrB_Info GrB_Matrix_select_INT64(GrB_Matrix C_, const GrB_Matrix M_, const GrB_B
     GB_Object *C = obj_check(C_, "C"), *A = obj_check(A_, "A");
     GB_Object *mask = M_ ? obj_check(M_, "mask") : nullptr;
     if (!op) grb_throw(GrB_NULL_POINTER, "op is NULL");
+    op_need_kernel(op->op, op->name);
     matrix_select(C, mask, accum_code_of(accum), op->op, A, y, desc_flags(desc));
     if (g.blocking) stream_sync();
     API_END(C_)

@@ -47,10 +47,12 @@ static void view_of(View &v, GB_Object *A, bool transpose) {
     else if (transpose) { mat_ensure_csc(A); v.csr = &A->csc; }
     else { mat_ensure_csr(A); v.csr = &A->csr; }
 }
-static void view_cast(View &v, int from_code, int to_code, size_t from_size) {
-    if (from_code == to_code) return;
+static void view_cast(View &v, int from_code, int to_code, size_t from_size, int via_code = -1) {
+    if (via_code == from_code) via_code = -1;
+    if (from_code == to_code && via_code < 0) return;
     Csr c = csr_dup(*v.csr, from_size);
-    csr_cast_values(c, from_code, to_code);
+    if (via_code >= 0) { csr_cast_values(c, from_code, via_code); csr_cast_values(c, via_code, to_code); }
+    else csr_cast_values(c, from_code, to_code);
     v.adopt(c);
 }
 
@@ -327,7 +329,12 @@ static void matrix_product(GB_Object *C, GB_Object *mask, const GrB_BinaryOp acc
     require_init();
     if (!sr) grb_throw(GrB_NULL_POINTER, "semiring is NULL");
     const int acc = accum_code_of(accum);
-    const int tcode = sr->tcode, mon = sr->mon, mul = sr->mul;
+    op_need_kernel(sr->mon, sr->name);
+    int tcode = sr->tcode, mul = sr->mul;
+    const int mon = sr->mon;
+    // INT8/INT16/UINT8/UINT16 semirings run in the 32-bit type of the same signedness (grb_internal.cuh)
+    int narrow = -1;
+    if (tc_is_narrow(tcode)) { narrow = tcode; mul = narrow_mul(mon, mul, narrow); tcode = tc_wide_of(narrow); }
     const bool uses_a = !(mul == OP_SECOND || mul == OP_ONEB), uses_b = !(mul == OP_FIRST || mul == OP_ONEB);
     View va, vb;
     view_of(va, A, f.tran0);
@@ -341,7 +348,7 @@ static void matrix_product(GB_Object *C, GB_Object *mask, const GrB_BinaryOp acc
                  (long long)k, (long long)vb.csr->nrows, (long long)n, (long long)crows, (long long)ccols, mask ? " (masked)" : "");
         grb_throw(GrB_DIMENSION_MISMATCH, b);
     }
-    if (uses_a) view_cast(va, A->type->code, tcode, A->type->size);
+    if (uses_a) view_cast(va, A->type->code, tcode, A->type->size, narrow);
     // ---- method: masked dot product when a non-complemented mask bounds the output ----
     bool use_dot = false;
     View vm;
@@ -358,14 +365,15 @@ static void matrix_product(GB_Object *C, GB_Object *mask, const GrB_BinaryOp acc
     if (use_dot) {
         View vbt;
         view_of(vbt, B, !f.tran1);   // rows of B' = columns of B
-        if (uses_b) view_cast(vbt, B->type->code, tcode, B->type->size);
+        if (uses_b) view_cast(vbt, B->type->code, tcode, B->type->size, narrow);
         const int m_vsize = f.structure ? 0 : (int)mask->type->size;
         const int m_fp = (mask->type->code == TC_FP32 || mask->type->code == TC_FP64);
         GRB_TYPE_SWITCH(tcode, TT, dot_typed<TT>(*vm.csr, m_vsize, m_fp, *va.csr, *vbt.csr, mon, mul, tcode, T));
     } else {
-        if (uses_b) view_cast(vb, B->type->code, tcode, B->type->size);
+        if (uses_b) view_cast(vb, B->type->code, tcode, B->type->size, narrow);
         GRB_TYPE_SWITCH(tcode, TT, gustavson_typed<TT>(*va.csr, *vb.csr, mon, mul, tcode, T));
     }
+    if (narrow >= 0) { csr_cast_values(T, tcode, narrow); tcode = narrow; }      // wrap to the semiring's own type
     mat_writeback(C, mask, f, acc, T, tcode, use_dot);
     if (g.blocking) stream_sync();
 }

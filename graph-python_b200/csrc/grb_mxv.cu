@@ -103,9 +103,11 @@ static void swap_pingpong(GB_Object *w) {
 template <class T>
 static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int mul, int tcode, GB_Object *Aobj,
                           bool use_transpose, const Csr *Aoverride, GB_Object *u, const void *u_vals,
-                          const DescFlags &f) {
+                          const DescFlags &f, int narrow = -1) {
+    // narrow >= 0: the semiring's type is that 8/16-bit integer type and T is its 32-bit stand-in (grb_internal.cuh):
+    // results always pass through a temporary and are wrapped to the narrow type before the write-back
     const int64_t n_out = w->nrows, n_in = u->nrows;
-    const bool fused = (w->type->code == tcode);
+    const bool fused = (w->type->code == tcode) && narrow < 0;
     const int64_t nu = vec_nvals(u);
     // ---- direction ----
     bool push = (nu * g.push_ratio < n_in);
@@ -118,7 +120,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     // A's values in the semiring's type; multiplies that ignore them (second, pair) never touch the pointer
     const bool uses_x = !(mul == OP_SECOND || mul == OP_ONEB);
     auto vals_of = [&](Csr *M) -> const T * {
-        return (const T *)(uses_x ? csr_vals_as(*M, Aobj->type->code, tcode) : M->vals);
+        return (const T *)(uses_x ? csr_vals_as(*M, Aobj->type->code, tcode, narrow) : M->vals);
     };
     auto get_csr = [&](bool want_transpose) -> Csr * {
         if (Aoverride) return nullptr;
@@ -138,7 +140,12 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         } else {
             int wcode = w->type->code;
             void *tc = dmalloc((size_t)(n_out > 0 ? n_out : 1) * w->type->size);
-            cast_array(tv, tcode, tc, wcode, n_out);
+            if (narrow >= 0 && wcode != narrow) {       // wrap to the semiring's own type first
+                void *tn = dmalloc((size_t)(n_out > 0 ? n_out : 1) * kTypeSize[narrow]);
+                cast_array(tv, tcode, tn, narrow, n_out);
+                cast_array(tn, narrow, tc, wcode, n_out);
+                dfree(tn);
+            } else cast_array(tv, tcode, tc, wcode, n_out);
             GRB_TYPE_SWITCH(wcode, W, {
                 EpiArgs<W> e = make_epi<W>(w, false, mask, f, accum);
                 GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, ew_grid4(n_out), 256, 0, e, (const W *)tc, tpres, n_out);
@@ -372,27 +379,38 @@ static void vector_product(GB_Object *w, GB_Object *mask, const GrB_BinaryOp acc
     }
     int acc = -1;
     if (accum) {
-        if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot accumulate into w");
+        op_need_kernel(accum->op, accum->name);
+        if (op_is_cmp(accum->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot accumulate into w");
         acc = accum->op;
     }
-    const int tcode = sr->tcode, mon = sr->mon;
+    op_need_kernel(sr->mon, sr->name);
+    int tcode = sr->tcode;
+    const int mon = sr->mon;
     int mul = sr->mul;
     // the kernels multiply (matrix entry, vector entry); vxm's multiply is (vector entry, matrix entry): swap the
     // operand-selecting and the non-commutative multiplies
     if (is_vxm) mul = (mul == OP_FIRST) ? OP_SECOND : (mul == OP_SECOND) ? OP_FIRST : (mul == OP_DIV) ? OP_RDIV : mul;
+    // INT8/INT16/UINT8/UINT16 semirings run in the 32-bit type of the same signedness (grb_internal.cuh)
+    int narrow = -1;
+    if (tc_is_narrow(tcode)) { narrow = tcode; mul = narrow_mul(mon, mul, narrow); tcode = tc_wide_of(narrow); }
     // pull reads rows of (is_vxm != tran) ? A' : A
     const bool use_transpose = (is_vxm != tran);
     // reconcile operand types with the semiring's type (cast copies; the common case needs none)
     void *u_cast = nullptr;
     const void *u_vals = u->vals;
-    if (u->type->code != tcode) {
+    if (u->type->code != tcode || narrow >= 0) {
         u_cast = dmalloc((size_t)(u->nrows > 0 ? u->nrows : 1) * kTypeSize[tcode]);
-        cast_array(u->vals, u->type->code, u_cast, tcode, u->nrows);
+        if (narrow >= 0 && u->type->code != narrow) {
+            void *un = dmalloc((size_t)(u->nrows > 0 ? u->nrows : 1) * kTypeSize[narrow]);
+            cast_array(u->vals, u->type->code, un, narrow, u->nrows);
+            cast_array(un, narrow, u_cast, tcode, u->nrows);
+            dfree(un);
+        } else cast_array(u->vals, u->type->code, u_cast, tcode, u->nrows);
         u_vals = u_cast;
     }
     // (A's values are cast inside product_typed, once per matrix: csr_vals_as)
     try {
-        GRB_TYPE_SWITCH(tcode, T, product_typed<T>(w, mask, acc, mon, mul, tcode, A, use_transpose, nullptr, u, u_vals, f));
+        GRB_TYPE_SWITCH(tcode, T, product_typed<T>(w, mask, acc, mon, mul, tcode, A, use_transpose, nullptr, u, u_vals, f, narrow));
     } catch (...) { dfree(u_cast); throw; }
     dfree(u_cast);
     if (g.blocking) stream_sync();
@@ -431,6 +449,7 @@ GrB_Info GrB_Matrix_reduce_Monoid(GrB_Vector w, const GrB_Vector mask, const GrB
     GB_Object *M = mask ? obj_check(mask, "mask") : nullptr;
     if (Aobj->kind != K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "A must be a matrix");
     const DescFlags f = desc_flags(desc);
+    op_need_kernel(monoid->op, monoid->name);
     const int tcode = monoid->tcode;
     GB_Semiring_opaque sr = {monoid->op, OP_FIRST, tcode, "reduce_rowwise"};
     bool fill = true;

@@ -61,7 +61,18 @@ template <class T> HD T op_div(T x, T y) {
     }
 }
 
-template <int OP, class T> struct BinOp;
+template <int ID> struct NarrowType;
+template <> struct NarrowType<NARROW_INT8> { using type = int8_t; };
+template <> struct NarrowType<NARROW_INT16> { using type = int16_t; };
+template <> struct NarrowType<NARROW_UINT8> { using type = uint8_t; };
+template <> struct NarrowType<NARROW_UINT16> { using type = uint16_t; };
+// primary template: a multiply that wraps to a narrow integer type (code = op | narrow id << 8, see grb_internal.cuh);
+// the built-in operators are the specialisations below
+template <int OP, class T> struct BinOp {
+    static_assert(OP >= 256, "unknown operator code");
+    using N = typename NarrowType<(OP >> 8)>::type;
+    static HD T apply(T x, T y) { return (T)BinOp<(OP & 255), N>::apply((N)x, (N)y); }
+};
 template <class T> struct BinOp<OP_FIRST, T> { static HD T apply(T x, T) { return x; } };
 template <class T> struct BinOp<OP_SECOND, T> { static HD T apply(T, T y) { return y; } };
 template <class T> struct BinOp<OP_ANY, T> { static HD T apply(T x, T) { return x; } };

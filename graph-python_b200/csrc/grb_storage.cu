@@ -177,14 +177,23 @@ void csr_drop_caches(Csr &c) {
 // Matrices are replaced (mat_set_csr) or, for GrB_Matrix_setElement on an existing entry, edited in place followed by
 // obj_invalidate_caches, so a typed copy of the values stays valid for the
 // life of the Csr: BOOL adjacency x INT32 vector products cast once, not per call.
-const void *csr_vals_as(Csr &c, int from_code, int to_code) {
-    if (from_code == to_code) return c.vals;
-    if (c.cast_vals && c.cast_code == to_code) return c.cast_vals;
+// via_code: cast through that type first (a narrow-integer semiring on a wider matrix: INT32 -> INT8 -> INT32)
+const void *csr_vals_as(Csr &c, int from_code, int to_code, int via_code) {
+    if (via_code == from_code) via_code = -1;
+    if (from_code == to_code && via_code < 0) return c.vals;
+    const int key = to_code | ((via_code + 1) << 8);
+    if (c.cast_vals && c.cast_code == key) return c.cast_vals;
     dfree(c.cast_vals);
     const int64_t n = c.iso ? 1 : c.nnz;
     c.cast_vals = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[to_code]);
-    cast_array(c.vals, from_code, c.cast_vals, to_code, n);
-    c.cast_code = to_code;
+    if (via_code < 0) cast_array(c.vals, from_code, c.cast_vals, to_code, n);
+    else {
+        void *mid = dmalloc((size_t)(n > 0 ? n : 1) * kTypeSize[via_code]);
+        cast_array(c.vals, from_code, mid, via_code, n);
+        cast_array(mid, via_code, c.cast_vals, to_code, n);
+        dfree(mid);
+    }
+    c.cast_code = key;
     return c.cast_vals;
 }
 void csr_free(Csr &c) {

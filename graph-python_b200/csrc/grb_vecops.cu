@@ -9,7 +9,8 @@ static inline int nblk(int64_t n, int b = 256) { return (int)cdiv(n > 0 ? n : 1,
 
 static int accum_code_of(const GrB_BinaryOp accum) {
     if (!accum) return -1;
-    if (accum->op >= OP_EQ) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
+    op_need_kernel(accum->op, accum->name);
+    if (op_is_cmp(accum->op)) grb_throw(GrB_DOMAIN_MISMATCH, "comparison operators cannot be accumulators");
     return accum->op;
 }
 static void need_vec(GB_Object *o, const char *what) {
@@ -173,6 +174,7 @@ GrB_Info GrB_Vector_apply(GrB_Vector w_, const GrB_Vector mask_, const GrB_Binar
     need_vec(w, "w"); need_vec(u, "u");
     const int64_t n = w->nrows;
     if (u->nrows != n || (mask && mask->nrows != n)) grb_throw(GrB_DIMENSION_MISMATCH, "apply: sizes differ");
+    op_need_kernel(op->op, op->name);
     const int tcode = op->tcode;
     void *uc = nullptr;
     const void *uv = u->vals;

@@ -60,6 +60,11 @@ class Op:
         self._typed = {}
 
     def _add(self, dtype, gb_name, return_type=None):
+        # the library exports both spellings of the official semirings (GrB_MIN_PLUS_SEMIRING_T and GxB_MIN_PLUS_T), as
+        # SuiteSparse does; the GrB_ handle wins, as in the reference (tests/test_op.py:88-91)
+        have = self._typed.get(dtype.name)
+        if have is not None and have.gb_name.startswith("GrB_") and gb_name.startswith("GxB_"):
+            return
         self._typed[dtype.name] = TypedOp(self, dtype, gb_name, return_type or dtype)
 
     @property

@@ -49,16 +49,41 @@ def test_binding_discovers_operators_by_name():
     assert semiring.any_pair["BOOL"].gb_name == "GxB_ANY_PAIR_BOOL"
     assert monoid.plus["FP64"].gb_name == "GrB_PLUS_MONOID_FP64"
     assert binary.plus["INT64"].gb_name == "GrB_PLUS_INT64"
-    with pytest.raises(KeyError):
-        semiring.plus_times["INT8"]  # no sm_100a kernel instantiated: must raise, not fall back
+    # INT8/INT16/UINT8/UINT16 semirings exist (computed in the 32-bit type, wrapped to the narrow one)
+    assert semiring.plus_times["INT8"]._carg == grb_b200.lib.GrB_PLUS_TIMES_SEMIRING_INT8
+    assert semiring.min_plus["UINT16"]._carg == grb_b200.lib.GrB_MIN_PLUS_SEMIRING_UINT16
 
 
-def test_udf_semiring_is_refused(dll):
+def test_semiring_new_composes_builtins_and_udfs_are_refused(dll):
+    """GrB_Semiring_new over built-in handles yields a handle (the reference's registry builds plus_pow & co at import,
+    graphblas/core/operator/semiring.py:370-390); user-defined FUNCTIONS are refused: no JIT, no CPU fallback."""
     import grb_b200
 
-    s = grb_b200.ffi.new("GrB_Semiring*")
-    assert grb_b200.lib.GrB_Semiring_new(s, grb_b200.lib.GrB_PLUS_MONOID_INT64, grb_b200.lib.GrB_TIMES_INT64) \
-        == grb_b200.lib.GrB_NOT_IMPLEMENTED
+    ffi, lib = grb_b200.ffi, grb_b200.lib
+    s = ffi.new("GrB_Semiring*")
+    assert lib.GrB_Semiring_new(s, lib.GrB_PLUS_MONOID_INT64, lib.GrB_TIMES_INT64) == lib.GrB_SUCCESS
+    assert s[0] != ffi.NULL
+    assert lib.GrB_Semiring_free(s) == lib.GrB_SUCCESS and s[0] == ffi.NULL
+    b = ffi.new("GrB_BinaryOp*")
+    assert lib.GrB_BinaryOp_new(b, ffi.NULL, lib.GrB_INT64, lib.GrB_INT64, lib.GrB_INT64) == lib.GrB_NOT_IMPLEMENTED
+    u = ffi.new("GrB_UnaryOp*")
+    assert lib.GrB_UnaryOp_new(u, ffi.NULL, lib.GrB_INT64, lib.GrB_INT64) == lib.GrB_NOT_IMPLEMENTED
+
+
+def test_registry_symbols_the_reference_scans_for(dll):
+    """Every name the reference's _parse_config regexes can match for non-complex types is exported
+    (graphblas/core/operator/{unary,binary,monoid,semiring,indexunary}.py), so `import graphblas` does not stop at a
+    missing attribute (round-1 probe: KeyError 'erf' at core/operator/unary.py:418)."""
+    for name in ("GxB_ERF_FP32", "GxB_LGAMMA_FP64", "GxB_SQRT_FP32", "GxB_ISNAN_FP64", "GrB_VALUENE_INT64",
+                 "GrB_VALUEEQ_BOOL", "GrB_ROWINDEX_INT64", "GrB_COLLE", "GrB_BOR_UINT8", "GxB_POW_FP64", "GxB_FIRSTI_INT64",
+                 "GxB_BSHIFT_INT8", "GxB_BOR_UINT32_MONOID", "GxB_EQ_BOOL_MONOID", "GxB_PLUS_RMINUS_FP32",
+                 "GxB_ANY_SECONDJ1_INT32", "GxB_LOR_GT_UINT8", "GxB_BOR_BAND_UINT64", "GxB_EQ_LXOR_BOOL",
+                 "GrB_PLUS_TIMES_SEMIRING_INT8", "GrB_MIN_PLUS_SEMIRING_UINT16", "GxB_PLUS_TIMES_INT32",
+                 "GxB_COMPRESSION_NONE", "GxB_SECURE_IMPORT", "GxB_Matrix_import_CSR", "GxB_Matrix_export_BitmapR",
+                 "GxB_Vector_import_CSC", "GxB_Vector_export_Full", "GxB_Matrix_pack_FullC"):
+        import grb_b200
+
+        assert hasattr(dll, name) or hasattr(grb_b200.lib, name), name
 
 
 def test_no_cpu_fallback_without_device():

@@ -232,3 +232,64 @@ def test_div_semirings_as_in_reference(gb):
     assert list(i) == [0] and list(x) == [8]
     i, x = B.T.mxv(u, semiring.plus_cdiv).new().to_coo()     # B(0,0)/u(0) + B(1,0)/u(1) = 0 + 0
     assert list(i) == [0] and list(x) == [0]
+
+
+def test_set_element_in_place_drops_value_caches(gb):
+    """GrB_Matrix_setElement on an existing entry edits the values in place; the typed copy of the
+    values (INT64 matrix under an FP64 semiring), the cached transpose and the stream form must not survive it."""
+    import numpy as np
+
+    from graphblas_b200 import Matrix, Vector, semiring
+    from oracle import oracle as O
+
+    scale = 9
+    n = 1 << scale
+    A = O.rmat_matrix(scale, "INT64", value_mode=1)
+    gA = Matrix.from_csr(A.indptr, A.indices, A.values, ncols=n)
+    x = np.random.default_rng(3).random(n)
+    gx = Vector.from_dense(x)
+    ox = O.Vec(x, np.ones(n, np.uint8), "FP64")
+    for tran in (False, True):
+        for _ in range(3):                      # the third pull runs on the cached stream form
+            (gA.T if tran else gA).mxv(gx, semiring.plus_times["FP64"]).new()
+    i = int(np.flatnonzero(np.diff(A.indptr) > 0)[5])
+    j = int(A.indices[A.indptr[i]])
+    gA[i, j] = 1000
+    A.values[A.indptr[i]] = 1000
+    for tran in (False, True):
+        w = O.Vec.empty(n, "FP64")
+        O.mxv(w, A, ox, "PLUS", "TIMES", "FP64", tran0=tran)
+        got = (gA.T if tran else gA).mxv(gx, semiring.plus_times["FP64"]).new()
+        vals, pres = got.to_dense()
+        p = w.present.astype(bool)
+        assert np.array_equal(pres.astype(bool), p)
+        assert np.allclose(vals[p], w.values[p], rtol=1e-12), tran
+
+
+def test_registry_only_operators_are_refused_at_call_time(gb):
+    """Handles that exist only so that python-graphblas's registry imports (tools/gen_abi.py registry_only_*) return
+    GrB_NOT_IMPLEMENTED when used: no silent fallback (north_star)."""
+    import grb_b200
+    from graphblas_b200 import Matrix, Vector
+
+    ffi, lib = grb_b200.ffi, grb_b200.lib
+    A = Matrix.from_coo([0, 1], [1, 0], [1, 2], nrows=2, ncols=2, dtype="INT64")
+    u = Vector.from_coo([0, 1], [3, 4], size=2, dtype="INT64")
+    w = Vector("INT64", 2)
+    assert lib.GrB_mxv(w._carg, ffi.NULL, ffi.NULL, lib.GxB_PLUS_RMINUS_INT64, A._carg, u._carg, ffi.NULL) == lib.GrB_NOT_IMPLEMENTED
+    msg = ffi.new("char**")
+    lib.GrB_Vector_error(msg, w._carg)
+    assert b"no sm_100a kernel" in ffi.string(msg[0])
+    assert lib.GrB_mxv(w._carg, ffi.NULL, lib.GxB_POW_INT64, lib.GrB_PLUS_TIMES_SEMIRING_INT64, A._carg, u._carg, ffi.NULL) \
+        == lib.GrB_NOT_IMPLEMENTED
+    assert lib.GrB_Vector_apply(w._carg, ffi.NULL, ffi.NULL, lib.GxB_SQRT_FP64, u._carg, ffi.NULL) == lib.GrB_NOT_IMPLEMENTED
+    # a semiring composed from built-ins with a kernel runs; one without is refused when used
+    s = ffi.new("GrB_Semiring*")
+    assert lib.GrB_Semiring_new(s, lib.GrB_MIN_MONOID_INT64, lib.GrB_PLUS_INT64) == lib.GrB_SUCCESS
+    assert lib.GrB_mxv(w._carg, ffi.NULL, ffi.NULL, s[0], A._carg, u._carg, ffi.NULL) == lib.GrB_SUCCESS
+    idx, vals = w.to_coo()
+    assert list(vals) == [5, 5]        # row 0: 1 + 4, row 1: 2 + 3
+    lib.GrB_Semiring_free(s)
+    assert lib.GrB_Semiring_new(s, lib.GrB_MIN_MONOID_INT64, lib.GrB_MINUS_INT64) == lib.GrB_SUCCESS
+    assert lib.GrB_mxv(w._carg, ffi.NULL, ffi.NULL, s[0], A._carg, u._carg, ffi.NULL) == lib.GrB_NOT_IMPLEMENTED
+    lib.GrB_Semiring_free(s)

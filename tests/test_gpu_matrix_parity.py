@@ -51,7 +51,9 @@ def test_device_rmat_equals_oracle_rmat(gb, scale, dt, vm, sym):
 
 SEMIRINGS = [("PLUS", "TIMES", "INT64"), ("PLUS", "TIMES", "FP64"), ("PLUS", "TIMES", "FP32"), ("MIN", "PLUS", "INT64"),
              ("PLUS", "PAIR", "INT64"), ("ANY", "PAIR", "BOOL"), ("LOR", "LAND", "BOOL"), ("MIN", "FIRST", "UINT64"),
-             ("MIN", "SECOND", "INT32"), ("MAX", "PLUS", "INT32"), ("PLUS", "SECOND", "FP32"), ("PLUS", "FIRST", "UINT32")]
+             ("MIN", "SECOND", "INT32"), ("MAX", "PLUS", "INT32"), ("PLUS", "SECOND", "FP32"), ("PLUS", "FIRST", "UINT32"),
+             # narrow integer types: 32-bit kernels, wrapped (see test_gpu_vector_parity.CASES)
+             ("PLUS", "TIMES", "INT8"), ("MIN", "PLUS", "UINT8"), ("MAX", "TIMES", "INT16"), ("PLUS", "PAIR", "UINT16")]
 
 
 @pytest.mark.parametrize("mon,mul,dt", SEMIRINGS)

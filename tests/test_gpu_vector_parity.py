@@ -43,6 +43,11 @@ CASES = [
     ("MIN", "FIRST", "UINT64"), ("MIN", "SECOND", "UINT32"), ("MAX", "PLUS", "INT32"), ("MAX", "MIN", "FP32"),
     ("ANY", "PAIR", "BOOL"), ("ANY", "PAIR", "INT32"), ("LOR", "LAND", "BOOL"), ("LXOR", "LAND", "BOOL"),
     ("MIN", "TIMES", "UINT32"), ("PLUS", "MIN", "INT64"),
+    # INT8 / INT16 / UINT8 / UINT16 (reference graphblas/core/operator/semiring.py:170-204): computed in 32 bits and wrapped;
+    # sums overflow the narrow type on purpose (255-valued weights), min_plus / max_times wrap inside the multiply
+    ("PLUS", "TIMES", "INT8"), ("PLUS", "TIMES", "UINT16"), ("MIN", "PLUS", "INT8"), ("MIN", "PLUS", "UINT16"),
+    ("MAX", "TIMES", "INT16"), ("MIN", "TIMES", "UINT8"), ("ANY", "PAIR", "UINT8"), ("MIN", "SECOND", "INT16"),
+    ("PLUS", "PAIR", "INT8"),
 ]
 
 

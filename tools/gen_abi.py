@@ -83,14 +83,76 @@ def semiring_name(mon, mul, t):
     return f"GxB_{mon}_{mul}_{t}"
 
 
+INTS = ["INT8", "INT16", "INT32", "INT64", "UINT8", "UINT16", "UINT32", "UINT64"]
+UINTS = ["UINT8", "UINT16", "UINT32", "UINT64"]
+NUM10 = [t for t, _, _ in NUMERIC]
+ALL11 = [t for t, _, _ in TYPES]
+NARROW = ["INT8", "INT16", "UINT8", "UINT16"]   # semirings computed in the 32-bit type, results wrapped to the narrow one
+
+
 def all_semirings():
+    """Semirings that have sm_100a kernels: (symbol, MON, MUL, TYPE).  Both spellings SuiteSparse exports
+    (GrB_<MON>_<MUL>_SEMIRING_<T> and GxB_<MON>_<MUL>_<T>) point at the same kernels."""
     out = []
     for mon, mul in SEMIRINGS_NUM:
-        for t in KERNEL_NUMERIC:
+        for t in KERNEL_NUMERIC + NARROW:
             out.append((semiring_name(mon, mul, t), mon, mul, t))
+            if (mon, mul) in GRB_SEMIRINGS:
+                out.append((f"GxB_{mon}_{mul}_{t}", mon, mul, t))
     for mon, mul in SEMIRINGS_BOOL:
         out.append((semiring_name(mon, mul, "BOOL"), mon, mul, "BOOL"))
+        if (mon, mul) in GRB_SEMIRINGS_BOOL:
+            out.append((f"GxB_{mon}_{mul}_BOOL", mon, mul, "BOOL"))
     return out
+
+
+def kernel_semirings():
+    """(MON, MUL, TYPE) triples the kernel translation units instantiate (wide types + BOOL)."""
+    seen, out = set(), []
+    for _, mon, mul, t in all_semirings():
+        if t in NARROW or (mon, mul, t) in seen:
+            continue
+        seen.add((mon, mul, t))
+        out.append((mon, mul, t))
+    # multiplies that wrap to a narrow integer type inside the 32-bit kernels (grb_internal.cuh: narrow_mul);
+    # N1..N4 = INT8, INT16, UINT8, UINT16
+    wide = {1: "INT32", 2: "INT32", 3: "UINT32", 4: "UINT32"}
+    for nid, t in wide.items():
+        for mon in ("MIN", "MAX"):
+            for mul in ("PLUS", "TIMES"):
+                out.append((mon, f"{mul}_N{nid}", t))
+        out.append(("PLUS", f"DIV_N{nid}", t))
+    return out
+
+
+def registry_only_semirings():
+    """Handles python-graphblas's registry finds by regex (reference graphblas/core/operator/semiring.py:170-204) that
+    have no kernel here: using one returns GrB_NOT_IMPLEMENTED (north_star: raise, no CPU fallback)."""
+    have = {n for n, *_ in all_semirings()}
+    out = []
+    muls = ["FIRST", "SECOND", "PAIR", "MIN", "MAX", "PLUS", "MINUS", "RMINUS", "TIMES", "DIV", "RDIV", "ISEQ", "ISNE",
+            "ISGT", "ISLT", "ISGE", "ISLE", "LOR", "LAND", "LXOR"]
+    for mon in ["MIN", "MAX", "PLUS", "TIMES", "ANY"]:
+        for mul in muls:
+            out += [f"GxB_{mon}_{mul}_{t}" for t in NUM10]
+        for mul in ["FIRSTI1", "FIRSTI", "FIRSTJ1", "FIRSTJ", "SECONDI1", "SECONDI", "SECONDJ1", "SECONDJ"]:
+            out += [f"GxB_{mon}_{mul}_{t}" for t in ("INT32", "INT64")]
+    for mon, mul in sorted(GRB_SEMIRINGS):
+        out += [f"GrB_{mon}_{mul}_SEMIRING_{t}" for t in NUM10]
+    for mon in ["LOR", "LAND", "LXOR", "EQ", "ANY"]:
+        for mul in ["EQ", "NE", "GT", "LT", "GE", "LE"]:
+            out += [f"GxB_{mon}_{mul}_{t}" for t in NUM10]
+        for mul in ["FIRST", "SECOND", "PAIR", "LOR", "LAND", "LXOR", "EQ", "GT", "LT", "GE", "LE"]:
+            out.append(f"GxB_{mon}_{mul}_BOOL")
+    for mon in ["BOR", "BAND", "BXOR", "BXNOR"]:
+        for mul in ["BOR", "BAND", "BXOR", "BXNOR"]:
+            out += [f"GxB_{mon}_{mul}_{t}" for t in UINTS]
+    seen, res = set(), []
+    for n in out:
+        if n not in have and n not in seen:
+            seen.add(n)
+            res.append(n)
+    return res
 
 
 def all_monoids():
@@ -102,7 +164,13 @@ def all_monoids():
         out.append((f"GxB_ANY_{t}_MONOID", "ANY", t))
     for mon in MONOIDS_BOOL:
         out.append((f"GrB_{mon}_MONOID_BOOL", mon, "BOOL"))
+    out.append(("GxB_EQ_BOOL_MONOID", "LXNOR", "BOOL"))      # eq on bool is lxnor
     return out
+
+
+def registry_only_monoids():
+    """reference graphblas/core/operator/monoid.py:179-195"""
+    return [f"GxB_{m}_{t}_MONOID" for m in ("BOR", "BAND", "BXOR", "BXNOR") for t in UINTS]
 
 
 UNOPS_T = [("IDENTITY", "GrB"), ("AINV", "GrB"), ("MINV", "GrB"), ("ABS", "GrB"), ("ONE", "GxB")]
@@ -120,6 +188,17 @@ def all_unops():
     return out
 
 
+def registry_only_unops():
+    """reference graphblas/core/operator/unary.py:142-167 (the GxB math set UnaryOp._initialize walks, :395-425)"""
+    out = [f"GxB_LNOT_{t}" for t in ALL11]
+    out += [f"GxB_{op}_{t}" for op in ("POSITIONI1", "POSITIONI", "POSITIONJ1", "POSITIONJ") for t in ("INT32", "INT64")]
+    math = ["SQRT", "LOG", "EXP", "LOG2", "SIN", "COS", "TAN", "ACOS", "ASIN", "ATAN", "SINH", "COSH", "TANH", "ACOSH",
+            "ASINH", "ATANH", "SIGNUM", "CEIL", "FLOOR", "ROUND", "TRUNC", "EXP2", "EXPM1", "LOG10", "LOG1P",
+            "LGAMMA", "TGAMMA", "ERF", "ERFC", "FREXPX", "FREXPE", "CBRT", "ISINF", "ISNAN", "ISFINITE"]
+    out += [f"GxB_{op}_{t}" for op in math for t in ("FP32", "FP64")]
+    return out
+
+
 def all_binops():
     out = []  # (symbol, OP, xtype, ztype)
     for op, pre in BINOPS_T:
@@ -130,6 +209,34 @@ def all_binops():
             out.append((f"{pre}_{op}_{t}", op, t, "BOOL"))
     for op in BOOLOPS:
         out.append((f"GrB_{op}", op, "BOOL", "BOOL"))
+    # SuiteSparse's typed logical ops (coerce to 0/1 in the operand type) and the reversed divide
+    for op in ("LOR", "LAND", "LXOR"):
+        for t, _, _ in TYPES:
+            out.append((f"GxB_{op}_{t}", op, t, t))
+    for t, _, _ in TYPES:
+        out.append((f"GxB_RDIV_{t}", "RDIV", t, t))
+    return out
+
+
+def registry_only_binops():
+    """reference graphblas/core/operator/binary.py:332-369"""
+    out = [f"GrB_{op}_{t}" for op in ("BOR", "BAND", "BXOR", "BXNOR") for t in INTS]
+    out += [f"GxB_{op}_{t}" for op in ("POW", "RMINUS", "ISEQ", "ISNE", "ISGT", "ISLT", "ISGE", "ISLE") for t in ALL11]
+    out += [f"GxB_{op}_{t}" for op in ("ATAN2", "HYPOT", "FMOD", "REMAINDER", "LDEXP", "COPYSIGN") for t in ("FP32", "FP64")]
+    out += [f"GxB_{op}_{t}" for op in ("BGET", "BSET", "BCLR", "BSHIFT") for t in INTS]
+    out += [f"GxB_{op}_{t}" for op in ("FIRSTI1", "FIRSTI", "FIRSTJ1", "FIRSTJ", "SECONDI1", "SECONDI", "SECONDJ1", "SECONDJ")
+            for t in ("INT32", "INT64")]
+    return out
+
+
+IDXOPS = ["TRIL", "TRIU", "DIAG", "OFFDIAG"]
+
+
+def registry_only_idxops():
+    """reference graphblas/core/operator/indexunary.py:98-113 (select.valuene is imported by core/mask.py:4)"""
+    out = [f"GrB_{op}_{t}" for op in ("ROWINDEX", "COLINDEX", "DIAGINDEX") for t in ("INT32", "INT64")]
+    out += [f"GrB_{op}" for op in ("COLLE", "COLGT", "ROWLE", "ROWGT")]
+    out += [f"GrB_{op}_{t}" for op in ("VALUEEQ", "VALUENE", "VALUEGT", "VALUEGE", "VALUELT", "VALUELE") for t in ALL11]
     return out
 
 
@@ -204,11 +311,24 @@ typedef enum {
 
 /* object / global options queried by the reference (graphblas/__init__.py:158, core/ss/matrix.py:216-220) */
 typedef enum {
-    GxB_HYPER_SWITCH = 0, GxB_FORMAT = 1, GxB_MODE = 2, GxB_SPARSITY_CONTROL = 32, GxB_SPARSITY_STATUS = 33,
-    GxB_BITMAP_SWITCH = 34
+    GxB_HYPER_SWITCH = 0, GxB_FORMAT = 1, GxB_MODE = 2, GxB_GLOBAL_NTHREADS = 5, GxB_GLOBAL_CHUNK = 7,
+    GxB_LIBRARY_NAME = 8, GxB_LIBRARY_VERSION = 9, GxB_LIBRARY_DATE = 10, GxB_LIBRARY_ABOUT = 11, GxB_LIBRARY_URL = 12,
+    GxB_LIBRARY_LICENSE = 13, GxB_LIBRARY_COMPILE_DATE = 14, GxB_LIBRARY_COMPILE_TIME = 15, GxB_API_VERSION = 16,
+    GxB_API_DATE = 17, GxB_API_ABOUT = 18, GxB_API_URL = 19, GxB_GLOBAL_GPU_CONTROL = 21, GxB_GLOBAL_GPU_CHUNK = 22,
+    GxB_COMPILER_VERSION = 23, GxB_COMPILER_NAME = 24, GxB_LIBRARY_OPENMP = 25,
+    GxB_SPARSITY_CONTROL = 32, GxB_SPARSITY_STATUS = 33, GxB_BITMAP_SWITCH = 34,
+    GxB_BURBLE = 99, GxB_PRINTF = 101, GxB_FLUSH = 102, GxB_MEMORY_POOL = 103, GxB_PRINT_1BASED = 104
 } GxB_Option_Field;
-typedef enum { GxB_BY_ROW = 0, GxB_BY_COL = 1 } GxB_Format_Value;
-enum { GxB_HYPERSPARSE = 1, GxB_SPARSE = 2, GxB_BITMAP = 4, GxB_FULL = 8 };
+typedef enum { GxB_BY_ROW = 0, GxB_BY_COL = 1, GxB_NO_FORMAT = -1 } GxB_Format_Value;
+enum { GxB_HYPERSPARSE = 1, GxB_SPARSE = 2, GxB_BITMAP = 4, GxB_FULL = 8, GxB_AUTO_SPARSITY = 15 };
+/* constants python-graphblas reads at import (graphblas/core/ss/descriptor.py:9-16, core/ss/config.py, core/ss/matrix.py) */
+enum { GxB_COMPRESSION_NONE = -1, GxB_COMPRESSION_DEFAULT = 0, GxB_COMPRESSION_LZ4 = 1000, GxB_COMPRESSION_LZ4HC = 2000,
+       GxB_COMPRESSION_ZSTD = 3000 };
+enum { GxB_FAST_IMPORT = 0, GxB_SECURE_IMPORT = 502 };
+enum { GxB_RANGE = 0, GxB_STRIDE = 1, GxB_BACKWARDS = 2, GxB_BEGIN = 0, GxB_END = 1, GxB_INC = 2 };
+enum { GxB_NBITMAP_SWITCH = 8, GxB_MAX_NAME_LEN = 128, GxB_FORMAT_DEFAULT = 0 };
+enum { GxB_GPU_ALWAYS = 2001, GxB_GPU_NEVER = 2002 };
+extern double GxB_HYPER_DEFAULT, GxB_ALWAYS_HYPER, GxB_NEVER_HYPER;   /* plain globals: cffi ABI mode cannot read const doubles */
 
 typedef struct GB_Type_opaque *GrB_Type;
 typedef struct GB_UnaryOp_opaque *GrB_UnaryOp;
@@ -245,9 +365,24 @@ GrB_Info GxB_Desc_set_INT32(GrB_Descriptor desc, GrB_Desc_Field field, int32_t v
 GrB_Info GrB_Descriptor_free(GrB_Descriptor *desc);
 GrB_Info GrB_Descriptor_error(const char **error, const GrB_Descriptor desc);
 
-/* ---- user-defined algebra: refused (north_star: UDF semirings raise, no CPU fallback) ---- */
+/* ---- algebra objects.  GrB_Semiring_new composes built-in monoids and multiplies (the reference's registry does so at
+ *      import, graphblas/core/operator/semiring.py:205-243); a triple without an instantiated kernel, and every
+ *      user-defined function, is refused with GrB_NOT_IMPLEMENTED when used (north_star: raise, no CPU fallback) ---- */
 GrB_Info GrB_Semiring_new(GrB_Semiring *semiring, GrB_Monoid add, GrB_BinaryOp multiply);
 GrB_Info GrB_Semiring_free(GrB_Semiring *semiring);
+GrB_Info GrB_UnaryOp_new(GrB_UnaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype);
+GrB_Info GrB_BinaryOp_new(GrB_BinaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype, GrB_Type ytype);
+GrB_Info GrB_IndexUnaryOp_new(GrB_IndexUnaryOp *op, void *function, GrB_Type ztype, GrB_Type xtype, GrB_Type ytype);
+GrB_Info GrB_UnaryOp_free(GrB_UnaryOp *op);
+GrB_Info GrB_BinaryOp_free(GrB_BinaryOp *op);
+GrB_Info GrB_IndexUnaryOp_free(GrB_IndexUnaryOp *op);
+GrB_Info GrB_Monoid_free(GrB_Monoid *op);
+GrB_Info GrB_Semiring_error(const char **error, const GrB_Semiring op);
+GrB_Info GrB_Monoid_error(const char **error, const GrB_Monoid op);
+GrB_Info GrB_BinaryOp_error(const char **error, const GrB_BinaryOp op);
+GrB_Info GrB_UnaryOp_error(const char **error, const GrB_UnaryOp op);
+GrB_Info GrB_IndexUnaryOp_error(const char **error, const GrB_IndexUnaryOp op);
+GrB_Info GrB_Type_error(const char **error, const GrB_Type t);
 
 /* ---- Matrix ---- */
 GrB_Info GrB_Matrix_new(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols);
@@ -404,6 +539,69 @@ GrB_Info GxB_Vector_pack_Bitmap(GrB_Vector v, int8_t **vb, void **vx, GrB_Index 
                                 bool iso, GrB_Index nvals, const GrB_Descriptor desc);
 GrB_Info GxB_Vector_unpack_Bitmap(GrB_Vector v, int8_t **vb, void **vx, GrB_Index *vb_size,
                                   GrB_Index *vx_size, bool *iso, GrB_Index *nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_pack_CSC(GrB_Vector v, GrB_Index **vi, void **vx, GrB_Index vi_size, GrB_Index vx_size, bool iso,
+                             GrB_Index nvals, bool jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_unpack_CSC(GrB_Vector v, GrB_Index **vi, void **vx, GrB_Index *vi_size, GrB_Index *vx_size, bool *iso,
+                               GrB_Index *nvals, bool *jumbled, const GrB_Descriptor desc);
+/* bitmap / full matrices (R = row-major, C = column-major host arrays); converted to CSR on the device, <= 2^31 cells */
+GrB_Info GxB_Matrix_pack_BitmapR(GrB_Matrix A, int8_t **Ab, void **Ax, GrB_Index Ab_size, GrB_Index Ax_size, bool iso,
+                                 GrB_Index nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_pack_BitmapC(GrB_Matrix A, int8_t **Ab, void **Ax, GrB_Index Ab_size, GrB_Index Ax_size, bool iso,
+                                 GrB_Index nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_unpack_BitmapR(GrB_Matrix A, int8_t **Ab, void **Ax, GrB_Index *Ab_size, GrB_Index *Ax_size, bool *iso,
+                                   GrB_Index *nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_unpack_BitmapC(GrB_Matrix A, int8_t **Ab, void **Ax, GrB_Index *Ab_size, GrB_Index *Ax_size, bool *iso,
+                                   GrB_Index *nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_pack_FullR(GrB_Matrix A, void **Ax, GrB_Index Ax_size, bool iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_pack_FullC(GrB_Matrix A, void **Ax, GrB_Index Ax_size, bool iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_unpack_FullR(GrB_Matrix A, void **Ax, GrB_Index *Ax_size, bool *iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_unpack_FullC(GrB_Matrix A, void **Ax, GrB_Index *Ax_size, bool *iso, const GrB_Descriptor desc);
+/* import = new + pack, export = unpack + free: what Matrix.ss.import_csr / Vector.ss.import_sparse / .ss.export call
+ * (graphblas/core/ss/matrix.py:879,920,1067-1069,1123-1125,1327,1517; core/ss/vector.py:530,568,601,991,1179,1341) */
+GrB_Info GxB_Matrix_import_CSR(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, GrB_Index **Ap,
+                               GrB_Index **Aj, void **Ax, GrB_Index Ap_size, GrB_Index Aj_size, GrB_Index Ax_size,
+                               bool iso, bool jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_import_CSC(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, GrB_Index **Ap,
+                               GrB_Index **Ai, void **Ax, GrB_Index Ap_size, GrB_Index Ai_size, GrB_Index Ax_size,
+                               bool iso, bool jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_CSR(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, GrB_Index **Ap,
+                               GrB_Index **Aj, void **Ax, GrB_Index *Ap_size, GrB_Index *Aj_size, GrB_Index *Ax_size,
+                               bool *iso, bool *jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_CSC(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, GrB_Index **Ap,
+                               GrB_Index **Ai, void **Ax, GrB_Index *Ap_size, GrB_Index *Ai_size, GrB_Index *Ax_size,
+                               bool *iso, bool *jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_import_BitmapR(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, int8_t **Ab, void **Ax,
+                                   GrB_Index Ab_size, GrB_Index Ax_size, bool iso, GrB_Index nvals,
+                                   const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_import_BitmapC(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, int8_t **Ab, void **Ax,
+                                   GrB_Index Ab_size, GrB_Index Ax_size, bool iso, GrB_Index nvals,
+                                   const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_BitmapR(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, int8_t **Ab,
+                                   void **Ax, GrB_Index *Ab_size, GrB_Index *Ax_size, bool *iso, GrB_Index *nvals,
+                                   const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_BitmapC(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, int8_t **Ab,
+                                   void **Ax, GrB_Index *Ab_size, GrB_Index *Ax_size, bool *iso, GrB_Index *nvals,
+                                   const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_import_FullR(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, void **Ax,
+                                 GrB_Index Ax_size, bool iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_import_FullC(GrB_Matrix *A, GrB_Type type, GrB_Index nrows, GrB_Index ncols, void **Ax,
+                                 GrB_Index Ax_size, bool iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_FullR(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, void **Ax,
+                                 GrB_Index *Ax_size, bool *iso, const GrB_Descriptor desc);
+GrB_Info GxB_Matrix_export_FullC(GrB_Matrix *A, GrB_Type *type, GrB_Index *nrows, GrB_Index *ncols, void **Ax,
+                                 GrB_Index *Ax_size, bool *iso, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_import_CSC(GrB_Vector *v, GrB_Type type, GrB_Index n, GrB_Index **vi, void **vx, GrB_Index vi_size,
+                               GrB_Index vx_size, bool iso, GrB_Index nvals, bool jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_export_CSC(GrB_Vector *v, GrB_Type *type, GrB_Index *n, GrB_Index **vi, void **vx, GrB_Index *vi_size,
+                               GrB_Index *vx_size, bool *iso, GrB_Index *nvals, bool *jumbled, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_import_Bitmap(GrB_Vector *v, GrB_Type type, GrB_Index n, int8_t **vb, void **vx, GrB_Index vb_size,
+                                  GrB_Index vx_size, bool iso, GrB_Index nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_export_Bitmap(GrB_Vector *v, GrB_Type *type, GrB_Index *n, int8_t **vb, void **vx, GrB_Index *vb_size,
+                                  GrB_Index *vx_size, bool *iso, GrB_Index *nvals, const GrB_Descriptor desc);
+GrB_Info GxB_Vector_import_Full(GrB_Vector *v, GrB_Type type, GrB_Index n, void **vx, GrB_Index vx_size, bool iso,
+                                const GrB_Descriptor desc);
+GrB_Info GxB_Vector_export_Full(GrB_Vector *v, GrB_Type *type, GrB_Index *n, void **vx, GrB_Index *vx_size, bool *iso,
+                                const GrB_Descriptor desc);
 GrB_Info GxB_Matrix_iso(bool *iso, const GrB_Matrix A);
 GrB_Info GxB_Vector_iso(bool *iso, const GrB_Vector v);
 /* copy-semantics dense hand-off used by the host mirror and the benchmark (host buffers stay the caller's) */
@@ -422,11 +620,19 @@ def emit_header():
     L.append("\n/* ---- built-in unary ops (apply) ---- */")
     L += [f"extern GrB_UnaryOp {n};" for n, *_ in all_unops()]
     L.append("\n/* ---- index-unary ops for select (tril/triu build the triangle-count input) ---- */")
-    L += [f"extern GrB_IndexUnaryOp GrB_{n};" for n in ("TRIL", "TRIU", "DIAG", "OFFDIAG")]
+    L += [f"extern GrB_IndexUnaryOp GrB_{n};" for n in IDXOPS]
     L.append("\n/* ---- built-in monoids ---- */")
     L += [f"extern GrB_Monoid {n};" for n, *_ in all_monoids()]
     L.append("\n/* ---- built-in semirings with sm_100a kernels (semiring.py:170-204 name patterns) ---- */")
     L += [f"extern GrB_Semiring {n};" for n, *_ in all_semirings()]
+    L.append("\n/* ---- operator handles the reference's registry discovers by regex over dir(lib)")
+    L.append(" *      (graphblas/core/operator/base.py:291,410-486) that have NO kernel in this library: they exist so that")
+    L.append(" *      `import graphblas` builds its namespaces; using one in a call returns GrB_NOT_IMPLEMENTED. ---- */")
+    L += [f"extern GrB_UnaryOp {n};" for n in registry_only_unops()]
+    L += [f"extern GrB_BinaryOp {n};" for n in registry_only_binops()]
+    L += [f"extern GrB_IndexUnaryOp {n};" for n in registry_only_idxops()]
+    L += [f"extern GrB_Monoid {n};" for n in registry_only_monoids()]
+    L += [f"extern GrB_Semiring {n};" for n in registry_only_semirings()]
     L.append("\n/* ---- predefined descriptors (graphblas/core/descriptor.py:51-87) ---- */")
     L += [f"extern GrB_Descriptor GrB_DESC_{d};" for d in DESC]
     L.append(HEADER_BOTTOM)
@@ -462,10 +668,15 @@ def emit_lists():
         L.append(f"    X({d}, {r}, {c}, {s}, {t0}, {t1}) \\")
     L.append("")
     # per-monoid semiring lists for the kernel instantiation units: X(MUL, TYPE)
-    mons = sorted({m for _, m, _, _ in all_semirings()})
+    mons = sorted({m for m, _, _ in kernel_semirings()})
     for mon in mons:
         L.append(f"#define GRB_SEMIRINGS_OF_{mon}(X) \\")
-        L += [f"    X({u}, {t}) \\" for _, m, u, t in all_semirings() if m == mon]
+        L += [f"    X({u}, {t}) \\" for m, u, t in kernel_semirings() if m == mon]
+        L.append("")
+    for name, fn in (("UNOP", registry_only_unops), ("BINOP", registry_only_binops), ("IDXOP", registry_only_idxops),
+                     ("MONOID", registry_only_monoids), ("SEMIRING", registry_only_semirings)):
+        L.append(f"#define GRB_{name}_STUB_LIST(X) \\")
+        L += [f"    X({n}) \\" for n in fn()]
         L.append("")
     return "\n".join(L) + "\n"
 
