@@ -470,6 +470,21 @@ GrB_Info GxB_b200_Matrix_rmat(GrB_Matrix *A, GrB_Type type, int scale, int edgef
                               int symmetrize, int value_mode);
 GrB_Info GxB_b200_rmat_edges_host(uint64_t *src, uint64_t *dst, int scale, uint64_t nedges, uint64_t seed);
 GrB_Info GxB_b200_Matrix_rowblock(GrB_Matrix *C, const GrB_Matrix A, GrB_Index row_begin, GrB_Index row_end);
+
+/* ---- allocation-free product.  No counterpart in the reference: added at the request of the run's operators for callers
+ *      that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *      w = A (+).(x) u, plus_times FP32, u full: a variant of the tiled pull kernel behind GrB_mxv whose scratch (tile table
+ *      and per-tile carries) is a file-scope static __device__ array instead of pool memory.  All pointers are DEVICE
+ *      pointers: rowptr int64[nrows+1], colidx uint32[nvals], values float[nvals], u float[ncols]; outputs w float[nrows]
+ *      and presence bytes w_present[nrows] (rows without entries are absent).  w_nvals (host, may be NULL) receives the
+ *      number of entries of w and makes the call synchronise.  Limit: nvals <= GXB_B200_NOALLOC_MAX_NVALS (2^26), else
+ *      GrB_INSUFFICIENT_SPACE and *error (host, may be NULL) points at a static message.  It calls no cudaMalloc/cudaFree
+ *      and no allocating library routine.  Every call shares the one scratch array (3.5 MB per GPU that loads the
+ *      library, until exit): calls that overlap on the GPU race; calls on the library's stream are ordered. ---- */
+#define GXB_B200_NOALLOC_MAX_NVALS 67108864
+GrB_Info GxB_b200_mxv_plus_times_FP32_noalloc(float *w, uint8_t *w_present, GrB_Index *w_nvals, const int64_t *rowptr,
+                                              const uint32_t *colidx, const float *values, const float *u,
+                                              GrB_Index nrows, GrB_Index ncols, GrB_Index nvals, const char **error);
 '''
 
 HEADER_BOTTOM = r'''/* cffi-end */
