@@ -38,7 +38,8 @@ void obj_release_storage(GB_Object *o) {
     csr_free(o->csr);
     if (o->csc_valid) csr_free(o->csc);
     o->csc_valid = false;
-    dfree(o->vals); dfree(o->present); dfree(o->vals_alt); dfree(o->present_alt); dfree(o->list);
+    if (!o->external_vals) dfree(o->vals);
+    dfree(o->present); dfree(o->vals_alt); dfree(o->present_alt); dfree(o->list);
     dfree(o->d_nvals);
     o->vals = o->vals_alt = nullptr; o->present = o->present_alt = nullptr; o->list = nullptr;
     o->d_nvals = nullptr; o->list_cap = 0; o->list_valid = false;
@@ -55,6 +56,9 @@ void vec_alloc(GB_Object *o) {
     o->nvals = 0; o->nvals_known = true; o->list_valid = false;
 }
 void vec_ensure_alt(GB_Object *o) {
+    if (o->external_vals)
+        grb_throw(GrB_NOT_IMPLEMENTED, "a vector that wraps caller-owned device memory cannot be the aliased output of a product "
+                                       "(its buffer would have to be swapped)");
     if (o->vals_alt) return;
     int64_t n = o->nrows;
     o->vals_alt = dmalloc((size_t)(n > 0 ? n : 1) * o->type->size);

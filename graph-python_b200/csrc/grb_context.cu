@@ -57,14 +57,14 @@ static GB_Type_opaque type_tab[TC_COUNT] = {
 // A ring of CUDA event pairs recorded on g.stream around each launch while g.timing != 0; folded into
 // per-name totals when the ring fills or when a total is read.  bench.py uses it for roofline.achieved.
 struct KtName { const char *name; double ms; uint64_t count; };
-struct KtPending { cudaEvent_t a, b; int name_idx; };
+struct KtPending { cudaEvent_t a, b; int name_idx; cudaStream_t stream; };
 static std::vector<KtName> kt_names;
 static std::vector<KtPending> kt_ring;
 static int kt_used = 0;
 static const int KT_RING = 2048;
 static void ktime_fold() {
     if (kt_used == 0) return;
-    cudaEventSynchronize(kt_ring[kt_used - 1].b);
+    for (int i = 0; i < kt_used; i++) cudaEventSynchronize(kt_ring[i].b);      // launches may sit on different streams
     for (int i = 0; i < kt_used; i++) {
         float ms = 0;
         if (cudaEventElapsedTime(&ms, kt_ring[i].a, kt_ring[i].b) == cudaSuccess) {
@@ -74,7 +74,7 @@ static void ktime_fold() {
     }
     kt_used = 0;
 }
-int ktime_begin(const char *name) {
+int ktime_begin(const char *name, cudaStream_t stream) {
     if ((int)kt_ring.size() < KT_RING) {
         kt_ring.resize(KT_RING);
         for (auto &p : kt_ring) { cudaEventCreate(&p.a); cudaEventCreate(&p.b); }
@@ -84,10 +84,12 @@ int ktime_begin(const char *name) {
     for (size_t i = 0; i < kt_names.size(); i++) if (kt_names[i].name == name || !strcmp(kt_names[i].name, name)) { idx = (int)i; break; }
     if (idx < 0) { kt_names.push_back({name, 0.0, 0}); idx = (int)kt_names.size() - 1; }
     kt_ring[kt_used].name_idx = idx;
-    cudaEventRecord(kt_ring[kt_used].a, g.stream);
+    kt_ring[kt_used].stream = stream;
+    cudaEventRecord(kt_ring[kt_used].a, stream);
     return kt_used++;
 }
-void ktime_end(int slot) { cudaEventRecord(kt_ring[slot].b, g.stream); }
+int ktime_begin(const char *name) { return ktime_begin(name, g.stream); }
+void ktime_end(int slot) { cudaEventRecord(kt_ring[slot].b, kt_ring[slot].stream); }
 
 extern "C" {
 #define X(NAME, CT, CODE) GrB_Type GrB_##NAME = &type_tab[CODE];
@@ -368,6 +370,7 @@ GrB_Info GxB_b200_set_option(const char *name, int64_t value) {
     else if (!strcmp(name, "push_edge_ratio")) { if (value < 0) return GrB_INVALID_VALUE; g.push_edge_ratio = value; }
     else if (!strcmp(name, "smem_kb")) { if (value < 64 || value > 226) return GrB_INVALID_VALUE; g.smem_kb = value; }
     else if (!strcmp(name, "timing")) { if (!value) ktime_fold(); g.timing = value; }
+    else if (!strcmp(name, "peer_carveout")) g.peer_carveout = value;
     else return GrB_INVALID_VALUE;
     return GrB_SUCCESS;
 }

@@ -103,6 +103,12 @@ struct Csr {
     // column panels (csr_ensure_panels): the same rows restricted to column ranges of `panel_width`, so that the
     // slice of the vector one pull gathers from stays L2-resident when the whole vector does not (multi-GPU row
     // blocks see all n columns).  Each panel is a full Csr with its own values (in type panel_code) and hub cache.
+    void *hub_vbuf = nullptr; uint8_t *hub_pbuf = nullptr; int64_t hub_buf_bytes = 0;   // this call's values at the hub columns (reused)
+    // per-tile row-block range + tiles per block of the stream form, for progress reporting (csr_ensure_tile_blocks)
+    uint32_t *tile_blocks = nullptr;
+    unsigned long long *tile_expected = nullptr;
+    int64_t tile_blocks_rpb = 0, tile_blocks_tstep = 0;
+    int tile_blocks_n = 0;
     Csr *panels = nullptr;
     int n_panels = 0;
     int panel_code = -1;
@@ -130,6 +136,7 @@ struct GB_Object {
     uint32_t *list = nullptr;        // sorted indices of present entries (sparse frontier), iff list_valid
     int64_t list_cap = 0;
     bool list_valid = false;
+    bool external_vals = false;      // vals belongs to the caller (GxB_b200_Vector_wrap_device): never freed, never swapped
     std::string err;
 };
 struct GB_Matrix_opaque : GB_Object {};
@@ -180,6 +187,11 @@ struct GrbGlobal {
     int64_t dot_hash = 1;          // masked dot product with a pair multiply: per-row hash sets instead of binary searches
     int64_t spgemm_panels = 1;     // SpGEMM heavy rows: shared-memory column panels (0 = per-CTA dense accumulator rows in HBM)
     int64_t timing = 0;            // record CUDA events around every launch (GxB_b200_kernel_time reads them)
+    int64_t peer_carveout = 86;    // preferred shared-memory carve-out (percent) of the fused peer exchange kernel: must match k_spmv_red's
+    // one-shot request set by GxB_b200_next_product_progress: the next k_spmv_red launch reports per-row-block progress
+    unsigned long long *progress_dev = nullptr, *progress_expected_dev = nullptr;
+    int progress_blocks = 0;
+    int64_t progress_rpb = 0;
     // scratch
     int64_t *d_scratch = nullptr;  // 64 int64 of device scratch (counters)
     int64_t *h_pinned = nullptr;   // 64 int64 of pinned host memory for small read-backs
@@ -187,6 +199,7 @@ struct GrbGlobal {
 extern GrbGlobal g;
 // per-kernel-name device timing (grb_context.cu): events on g.stream around each launch while g.timing is set
 int ktime_begin(const char *name);
+int ktime_begin(const char *name, cudaStream_t stream);   // a launch on another stream (grb_peer.cu)
 void ktime_end(int slot);
 
 // every kernel launch goes through this macro: counts launches (bench.py's gpu_launches) and names the path
@@ -240,7 +253,8 @@ void vec_build_list(GB_Object *o);                        // dense -> sorted ind
 void mat_ensure_csc(GB_Object *o);                        // build + cache the transpose on the device
 void csr_transpose(const Csr &a, Csr &t, size_t tsize);
 void csr_ensure_tiles(Csr &c, int tile_nnz);
-void csr_ensure_hubs(Csr &c, int capacity);               // build / rebuild the hub cache for at most `capacity` hubs
+void csr_ensure_hubs(Csr &c, int capacity);
+void csr_ensure_tile_blocks(Csr &c, int64_t rows_per_block, int nblocks, int64_t tstep);   // needs the stream form (csr_ensure_hubs)               // build / rebuild the hub cache for at most `capacity` hubs
 void csr_ensure_panels(Csr &c, int npanels, const void *vals, int tcode);   // split by column ranges (values in tcode)
 void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)
 const void *csr_vals_as(Csr &c, int from_code, int to_code, int via_code = -1);   // c.vals, or a cached typed copy of them

@@ -100,10 +100,13 @@ static void swap_pingpong(GB_Object *w) {
 // t = M (+).(x) u computed into (w or a temporary) with the requested write-back.
 //   Mpull: CSR whose rows are indexed by the OUTPUT index (used by pull)
 //   Mpush: CSR whose rows are indexed by u's index        (used by push); fetched lazily through getters
+// one-shot request of GxB_b200_next_product_progress, taken over by the product that follows it
+struct ProgressReq { unsigned long long *counters = nullptr, *expected = nullptr; int nblocks = 0; int64_t rpb = 0; };
+
 template <class T>
 static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int mul, int tcode, GB_Object *Aobj,
                           bool use_transpose, const Csr *Aoverride, GB_Object *u, const void *u_vals,
-                          const DescFlags &f, int narrow = -1) {
+                          const DescFlags &f, int narrow = -1, ProgressReq prog = ProgressReq()) {
     // narrow >= 0: the semiring's type is that 8/16-bit integer type and T is its 32-bit stand-in (grb_internal.cuh):
     // results always pass through a temporary and are wrapped to the narrow type before the write-back
     const int64_t n_out = w->nrows, n_in = u->nrows;
@@ -111,9 +114,12 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     const int64_t nu = vec_nvals(u);
     // ---- direction ----
     bool push = (nu * g.push_ratio < n_in);
+    if (prog.counters) push = false;      // progress is reported by the tiled pull only
     if (g.force_direction == 1) push = false;
     if (g.force_direction == 2) push = true;
     if (nu == 0) push = true;   // nothing to multiply: the scatter is skipped, only the write-back runs
+    if (prog.counters && push)
+        grb_throw(GrB_NOT_IMPLEMENTED, "progress reporting (GxB_b200_next_product_progress) needs a non-empty, full input vector");
     const bool any_mon = (mon == OP_ANY);
     const bool have_mask = (mask != nullptr);
 
@@ -223,7 +229,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     }
     if (use_stream) {
         M->pull_uses++;
-        const bool build = g.hub_mode >= 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20));
+        const bool build = g.hub_mode >= 2 || (M->pull_uses >= 2 && M->nnz >= (1 << 20)) || prog.counters != nullptr;
         if (npanels > 1) {
             if (build) {
                 csr_ensure_panels(*M, npanels, uses_x ? (const void *)a.av : nullptr, tcode);
@@ -241,12 +247,24 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
     // partial sums go straight into w; any other write-back (mask, replace, foreign accumulator, type cast) first
     // reduces into a temporary t and then runs the dense C-API write-back over it: 190 + 20 us against 380-450 us
     // for the scan-based k_spmv_stream + fix-up passes on the PageRank graph (tools/debug/masked_variants.py).
+    if (prog.counters && !(use_stream && red_shape && fused && npanels == 1 && a.up == nullptr && nu > 0))
+        grb_throw(GrB_NOT_IMPLEMENTED, "progress reporting (GxB_b200_next_product_progress) needs the unmasked pull `w(monoid) << A.mxv(u)` "
+                                       "with u full, w of the semiring's type and a matrix that fits one column panel");
     if (use_stream && (red_shape || g.hub_mode != 3)) {
         const bool direct = fused && red_shape;
         const bool pingpong = direct && ((w == u) || (u_vals == w->vals));
         RedArgs<T> ra;
         ra.u = (const T *)u_vals; ra.up = a.up; ra.flags = (int)g.red_flags;
         ra.upairs = nullptr;
+        ra.progress = nullptr; ra.tile_blocks = nullptr; ra.stamps = nullptr;
+        if (prog.counters) {
+            // warps of the launch below (grb_spmv_inst.inc: launch_red_v): min(ceil(tiles / W), SMs) CTAs of W warps
+            const int64_t W = sizeof(T) > 4 ? RED_WARPS_8B : 32, want = cdiv(M->n_stiles, W);
+            csr_ensure_tile_blocks(*M, prog.rpb, prog.nblocks, (want < g.sm_count ? (want > 0 ? want : 1) : g.sm_count) * W);
+            ra.progress = prog.counters; ra.tile_blocks = M->tile_blocks;
+            ra.stamps = prog.counters + prog.nblocks;       // the caller's counter array has two spare words behind the blocks
+            if (prog.expected) d2d(prog.expected, M->tile_expected, (size_t)prog.nblocks * 8);
+        }
         if (ra.up) {      // sparse u: interleave (value, presence) so that one gather fetches both
             pair_bits_t<T> *pairs = (pair_bits_t<T> *)dmalloc((size_t)n_in * sizeof(pair_bits_t<T>));
             GRB_LAUNCH("pack_pairs", k_pack_pairs<T>, ew_grid(n_in), 256, 0, ra.u, ra.up, n_in, pairs);
@@ -254,7 +272,8 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         }
         const T ident = monoid_identity<T>(mon);
         const bool overwrite = !direct || accum < 0;
-        const bool w_full = direct && w->nvals_known && w->nvals == n_out;
+        // (a vector wrapped over caller-owned memory is full by contract, GxB_b200_Vector_wrap_device: its count is never lost)
+        const bool w_full = direct && (w->external_vals || (w->nvals_known && w->nvals == n_out));
         if (direct) {
             if (pingpong) {
                 vec_ensure_alt(w);
@@ -275,11 +294,17 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
             if (Mp->nnz == 0) continue;
             ra.pcol = Mp->hub_col; ra.av = npanels > 1 ? (const T *)Mp->vals : a.av; ra.a_iso = Mp->iso;
             ra.hub_n = Mp->hub_n; ra.nzrow = Mp->nzrow; ra.chunk_first = Mp->chunk_first; ra.nnz = Mp->nnz; ra.ntiles = Mp->n_stiles;
-            T *hv = dalloc<T>(ra.hub_n); uint8_t *hp = dalloc<uint8_t>(ra.hub_n);
+            // the hub values of this call live in a buffer kept with the matrix: no stream-ordered free between the product and
+            // whatever the caller launches right behind it (the fused peer exchange relies on being the next node in the stream)
+            if (Mp->hub_buf_bytes < (int64_t)ra.hub_n * (int64_t)sizeof(T) || !Mp->hub_vbuf) {
+                dfree(Mp->hub_vbuf); dfree(Mp->hub_pbuf);
+                Mp->hub_buf_bytes = (int64_t)ra.hub_n * 8;
+                Mp->hub_vbuf = dmalloc((size_t)Mp->hub_buf_bytes); Mp->hub_pbuf = dalloc<uint8_t>(ra.hub_n);
+            }
+            T *hv = (T *)Mp->hub_vbuf; uint8_t *hp = Mp->hub_pbuf;
             GRB_LAUNCH("gather_hubs", k_gather_hubs<T>, nblk(ra.hub_n), 256, 0, ra.u, ra.up, Mp->hub_ids, ra.hub_n, hv, hp);
             ra.hub_v = hv; ra.hub_p = hp;
             ok = spmv_launch_red(mon, mul, tcode, &ra);
-            dfree(hv); dfree(hp);
         }
         dfree((void *)ra.upairs);
         if (!ok) { dfree(t); dfree(tp); grb_throw(GrB_NOT_IMPLEMENTED, "semiring has no sm_100a kernel"); }
@@ -355,6 +380,9 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
 static void vector_product(GB_Object *w, GB_Object *mask, const GrB_BinaryOp accum, const GrB_Semiring sr,
                            GB_Object *A, GB_Object *u, const DescFlags &f, bool is_vxm) {
     require_init();
+    ProgressReq prog;
+    prog.counters = g.progress_dev; prog.expected = g.progress_expected_dev; prog.nblocks = g.progress_blocks; prog.rpb = g.progress_rpb;
+    g.progress_dev = nullptr; g.progress_expected_dev = nullptr;       // consumed by this product, whatever happens to it
     if (!sr) grb_throw(GrB_NULL_POINTER, "semiring is NULL");
     if (w->kind == K_MATRIX || u->kind == K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "w and u must be vectors");
     if (mask && mask->kind == K_MATRIX) grb_throw(GrB_INVALID_OBJECT, "mask must be a vector");
@@ -410,7 +438,7 @@ static void vector_product(GB_Object *w, GB_Object *mask, const GrB_BinaryOp acc
     }
     // (A's values are cast inside product_typed, once per matrix: csr_vals_as)
     try {
-        GRB_TYPE_SWITCH(tcode, T, product_typed<T>(w, mask, acc, mon, mul, tcode, A, use_transpose, nullptr, u, u_vals, f, narrow));
+        GRB_TYPE_SWITCH(tcode, T, product_typed<T>(w, mask, acc, mon, mul, tcode, A, use_transpose, nullptr, u, u_vals, f, narrow, prog));
     } catch (...) { dfree(u_cast); throw; }
     dfree(u_cast);
     if (g.blocking) stream_sync();

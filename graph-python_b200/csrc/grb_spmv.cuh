@@ -677,6 +677,9 @@ template <class T> struct RedArgs {
     int64_t nnz, ntiles;
     T *w; uint8_t *wp;            // wp == nullptr: presence is already known to be all ones
     int flags;                    // bit 0: load tiles directly instead of by TMA (option red_flags = 1, for A/B measurements)
+    unsigned long long *progress; // optional: per row block, the number of finished tiles that touch it (monotonic)
+    const uint32_t *tile_blocks;  // [ntiles] first block | last block << 16 of each tile (csr_ensure_tile_blocks)
+    unsigned long long *stamps;   // optional debugging aid: [0] = first CTA's start, [1] = last warp's end (globaltimer ns)
 };
 template <class T> static inline int red_warps() { return sizeof(T) > 4 ? RED_WARPS_8B : 32; }
 // shared memory: hub table | per-warp stage (256 x (4 + sizeof(T)) bytes, filled by TMA bulk copies) | mbarriers
@@ -718,7 +721,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // carve-out (28 KB L1) the same kernel runs 1.3-1.5x slower than with <= 196 KB (60 KB L1), although the table
 // is 20% smaller.  Issuing the next tile's gathers ahead of the reduction (look-ahead) made it slower at every
 // budget for the same reason, so each warp keeps exactly one tile in flight.
-template <class SR, int WARPS, bool SPARSE>
+// one warp reports "I am done with row blocks lo..hi" (see k_spmv_red)
+__device__ __forceinline__ void red_report(unsigned long long *progress, uint32_t lo, uint32_t hi, int lane) {
+    if (lo > hi) return;
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence();
+        for (uint32_t b = lo; b <= hi; b++) atomicAdd(progress + b, 1ull);
+    }
+}
+
+template <class SR, int WARPS, bool SPARSE, bool PROGRESS = false>
 __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR::type> a) {
     using T = typename SR::type;
     using Mon = typename SR::Mon;
@@ -745,6 +758,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
     if (lane == 0) mbar_init(bar_a, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
+    // programmatic dependent launch: a kernel launched right behind this one with the programmatic-serialization attribute
+    // (the fused peer exchange, grb_peer.cu) may start now, i.e. only once every CTA of this grid is resident -- the exchange
+    // spins on this kernel's progress counters, so it must never occupy an SM before this kernel does.  No-op otherwise.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const unsigned FULLM = 0xffffffffu;
     const bool stage_vals = kStageVals && !a.a_iso;
     const int64_t nfull = (a.flags & 1) ? 0 : a.nnz / ST_TILE;   // tiles that arrive by bulk copy; a ragged last tile is loaded directly
@@ -758,7 +775,25 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
     };
     if (lane == 0 && t < nfull) issue(t);
     uint32_t parity = 0;
+    // progress reporting (multi-GPU exchange, grb_peer.cu): a warp's tiles ascend through the rows, so when it starts a tile
+    // whose first row block is b0, it is done with every block below b0: it then counts itself once into each such block it
+    // touched (one fence per block transition, i.e. a handful per warp -- a fence per tile made the kernel 3x slower).  A
+    // block is complete when as many warps as touch it (csr_ensure_tile_blocks: `expected`) have reported.
+    // PROGRESS is a compile-time variant (8 more registers, which the co-resident exchange kernel needs): the plain kernel is
+    // untouched.  The block range of the NEXT tile is fetched one tile ahead: a warp has one tile in flight, so a dependent
+    // load at the top of every tile costs its full latency (262 vs 199 us measured, profiles/r02i_*).
+    uint32_t pend_lo = 0xffffffffu, pend_hi = 0, tb_next = 0;
+    if (PROGRESS) tb_next = (t < a.ntiles) ? a.tile_blocks[t] : 0u;
+    if (PROGRESS && a.stamps && blockIdx.x == 0 && tid == 0) { unsigned long long now; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now)); a.stamps[0] = now; a.stamps[1] = 0; }
     for (; t < a.ntiles; t += tstep) {
+        if (PROGRESS) {
+            const uint32_t tb = tb_next, b0 = tb & 0xffffu, b1 = tb >> 16;
+            tb_next = (t + tstep < a.ntiles) ? a.tile_blocks[t + tstep] : 0u;
+            if (pend_lo < b0) { red_report(a.progress, pend_lo, pend_hi < b0 - 1 ? pend_hi : b0 - 1, lane); pend_lo = b0; }
+            pend_lo = pend_lo < b0 ? pend_lo : b0;
+            pend_hi = pend_hi > b1 ? pend_hi : b1;
+        }
+      do {
         const int64_t chunk = t * 32 + lane;
         const int64_t p0 = chunk * ST_EPL;
         const bool tile_full = t < nfull;
@@ -869,9 +904,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
                 Mon::atomic(a.w + r0, acc);
                 if (a.wp && (SPARSE || (fbits & 1u))) a.wp[r0] = 1;
             }
-            continue;
+            break;
         }
-        if (nvalid == 0) continue;
+        if (nvalid == 0) break;
         if (!SPARSE && a.wp && (fbits & 1u)) a.wp[r0] = 1;
         int m = 0;
         uint32_t r = r0;
@@ -894,7 +929,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k_spmv_red(RedArgs<typename SR:
             Mon::atomic(a.w + r, acc);
             if (SPARSE && a.wp) a.wp[r] = 1;
         }
+      } while (0);
     }
+    if (PROGRESS) red_report(a.progress, pend_lo, pend_hi, lane);     // whatever this warp still owes
+    if (PROGRESS && a.stamps && lane == 0) { unsigned long long now; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now)); atomicMax(a.stamps + 1, now); }
 }
 
 // w := identity where absent (accumulating call) or everywhere with presence cleared (overwriting call)

@@ -171,6 +171,8 @@ void csr_drop_caches(Csr &c) {
     dfree(c.nzrow); dfree(c.tile_first); dfree(c.chunk_first); c.nzrow = nullptr; c.tile_first = nullptr; c.chunk_first = nullptr;
     c.n_nzrow = 0; c.n_stiles = 0;
     dfree(c.cast_vals); c.cast_vals = nullptr; c.cast_code = -1;
+    dfree(c.hub_vbuf); dfree(c.hub_pbuf); c.hub_vbuf = nullptr; c.hub_pbuf = nullptr; c.hub_buf_bytes = 0;
+    dfree(c.tile_blocks); dfree(c.tile_expected); c.tile_blocks = nullptr; c.tile_expected = nullptr; c.tile_blocks_rpb = 0; c.tile_blocks_n = 0;
     for (int p = 0; p < c.n_panels; p++) csr_free(c.panels[p]);
     delete[] c.panels; c.panels = nullptr; c.n_panels = 0; c.panel_code = -1; c.panel_width = 0;
 }
@@ -200,6 +202,48 @@ void csr_free(Csr &c) {
     csr_drop_caches(c);
     dfree(c.rowptr); dfree(c.colidx); dfree(c.vals);
     c = Csr();
+}
+
+// ---------------------------------------------------------------- progress table of the stream form
+// tile t of the flagged stream covers entries [256 t, 256 t + 256): which row blocks (of rows_per_block rows) do its rows lie in?
+__global__ void k_tile_blocks(const uint32_t *pcol, const uint32_t *nzrow, const uint32_t *chunk_first, int64_t nnz, int64_t ntiles,
+                              int64_t rpb, uint32_t *tile_blocks, unsigned long long *expected) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const int64_t e0 = t * 256, e1 = (e0 + 256 < nnz ? e0 + 256 : nnz) - 1;
+    const uint32_t first_row = nzrow[chunk_first[e0 >> 3]];
+    uint32_t j1 = chunk_first[e1 >> 3];
+    for (int64_t e = (e1 & ~(int64_t)7) + 1; e <= e1; e++) j1 += (pcol[e] >> 30) & 1u;      // row starts after the chunk's first entry
+    const uint32_t last_row = nzrow[j1];
+    const uint32_t b0 = (uint32_t)(first_row / rpb), b1 = (uint32_t)(last_row / rpb);
+    tile_blocks[t] = b0 | (b1 << 16);
+}
+// expected[b] = number of warps (out of `tstep` = grid x warps-per-CTA, tiles dealt round-robin) that touch row block b
+__global__ void k_tile_expected(const uint32_t *tile_blocks, int64_t ntiles, int64_t tstep, unsigned long long *expected) {
+    const int64_t w = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (w >= tstep) return;
+    int64_t done_below = -1;            // blocks <= done_below are already counted for this warp
+    for (int64_t t = w; t < ntiles; t += tstep) {
+        const uint32_t tb = tile_blocks[t];
+        int64_t b0 = tb & 0xffffu;
+        const int64_t b1 = tb >> 16;
+        if (b0 <= done_below) b0 = done_below + 1;
+        for (int64_t b = b0; b <= b1; b++) atomicAdd(expected + b, 1ull);
+        if (b1 > done_below) done_below = b1;
+    }
+}
+void csr_ensure_tile_blocks(Csr &c, int64_t rpb, int nblocks, int64_t tstep) {
+    if (c.tile_blocks && c.tile_blocks_rpb == rpb && c.tile_blocks_n == nblocks && c.tile_blocks_tstep == tstep) return;
+    if (!c.hub_col || !c.nzrow || !c.chunk_first) grb_throw(GrB_INVALID_OBJECT, "progress table: the stream form of the matrix is missing");
+    if (nblocks < 1 || nblocks > 65535 || rpb < 1 || cdiv(c.nrows, rpb) > nblocks) grb_throw(GrB_INVALID_VALUE, "progress table: bad row blocks");
+    dfree(c.tile_blocks); dfree(c.tile_expected);
+    c.tile_blocks = dalloc<uint32_t>(c.n_stiles);
+    c.tile_expected = dalloc<unsigned long long>(nblocks);
+    dzero(c.tile_expected, (size_t)nblocks * 8);
+    GRB_LAUNCH("tile_blocks", k_tile_blocks, nblk(c.n_stiles), 256, 0, c.hub_col, c.nzrow, c.chunk_first, c.nnz, c.n_stiles, rpb,
+               c.tile_blocks, c.tile_expected);
+    GRB_LAUNCH("tile_expected", k_tile_expected, nblk(tstep), 256, 0, c.tile_blocks, c.n_stiles, tstep, c.tile_expected);
+    c.tile_blocks_rpb = rpb; c.tile_blocks_n = nblocks; c.tile_blocks_tstep = tstep;
 }
 
 // ---------------------------------------------------------------- column panels

@@ -517,6 +517,14 @@ class Vector(BaseType):
         super().__init__(_free_later(gb_obj, "GrB_Vector_free"), dtype, name)
         self._size = int(size)
 
+    @classmethod
+    def _from_handle(cls, gb_obj, dtype, size, name=None):
+        """Adopt a GrB_Vector* made by a library call (GxB_b200_Vector_wrap_device); freed with GrB_Vector_free."""
+        out = object.__new__(cls)
+        BaseType.__init__(out, _free_later(gb_obj, "GrB_Vector_free"), lookup_dtype(dtype), name)
+        out._size = int(size)
+        return out
+
     @property
     def size(self):
         return self._size

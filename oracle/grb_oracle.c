@@ -341,3 +341,117 @@ void orc_rmat_edges(int scale, uint64_t nedges, uint64_t seed, uint64_t *src, ui
         dst[e] = rmat_permute(c, scale, seed);
     }
 }
+
+/* ---------- the same graph straight into CSR, in parallel (bench.py's CPU arm at scale 23-26, where the numpy path
+ * np.unique(keys) of oracle.py:rmat_pattern takes minutes) ----------
+ * Result == oracle.py:rmat_pattern(scale, edgefactor, seed, symmetrize) laid out by rows (transpose = 0) or by columns
+ * (transpose = 1: rows of the result are the edges' destinations): self-loops dropped, duplicates collapsed, columns
+ * sorted.  tests/test_oracle_golden.py checks it against the numpy path.  Buffers are malloc'd: release with orc_free. */
+static int cmp_u32(const void *a, const void *b) {
+    uint32_t x = *(const uint32_t *)a, y = *(const uint32_t *)b;
+    return x < y ? -1 : (x > y);
+}
+int orc_rmat_csr(int scale, uint64_t nedges, uint64_t seed, int transpose, int symmetrize, int64_t **Ap_out,
+                 int64_t **Aj_out, int64_t *nnz_out) {
+    if (scale < 1 || scale > 31) return -1;
+    const int64_t n = (int64_t)1 << scale, ne = (int64_t)nedges;
+    uint32_t *R = (uint32_t *)malloc((size_t)ne * 4), *C = (uint32_t *)malloc((size_t)ne * 4);
+    int64_t *start = (int64_t *)calloc((size_t)n + 1, 8), *cursor = (int64_t *)malloc((size_t)(n + 1) * 8);
+    if (!R || !C || !start || !cursor) { free(R); free(C); free(start); free(cursor); return -2; }
+    const uint64_t TA = 2448131358ull, TAB = 3264175144ull, TABC = 4080218931ull;
+#pragma omp parallel for schedule(static)
+    for (int64_t e = 0; e < ne; e++) {
+        uint64_t st = splitmix64(seed ^ ((uint64_t)e * 0xD1342543DE82EF95ull));
+        uint64_t r = 0, c = 0;
+        for (int l = 0; l < scale; l++) {
+            uint64_t u = splitmix64(st + (uint64_t)l) >> 32;
+            uint64_t rb = (u >= TAB), cb = (u >= TA && u < TAB) || (u >= TABC);
+            r = (r << 1) | rb; c = (c << 1) | cb;
+        }
+        const uint32_t s = (uint32_t)rmat_permute(r, scale, seed), d = (uint32_t)rmat_permute(c, scale, seed);
+        R[e] = transpose ? d : s;
+        C[e] = transpose ? s : d;
+        if (s != d) {
+#pragma omp atomic
+            start[R[e] + 1]++;
+            if (symmetrize) {
+#pragma omp atomic
+                start[C[e] + 1]++;
+            }
+        }
+    }
+    for (int64_t i = 0; i < n; i++) start[i + 1] += start[i];
+    memcpy(cursor, start, (size_t)(n + 1) * 8);
+    const int64_t total = start[n];
+    uint32_t *col = (uint32_t *)malloc((size_t)(total > 0 ? total : 1) * 4);
+    if (!col) { free(R); free(C); free(start); free(cursor); return -2; }
+#pragma omp parallel for schedule(static)
+    for (int64_t e = 0; e < ne; e++) {
+        if (R[e] == C[e]) continue;
+        int64_t p;
+#pragma omp atomic capture
+        p = cursor[R[e]]++;
+        col[p] = C[e];
+        if (symmetrize) {
+#pragma omp atomic capture
+            p = cursor[C[e]]++;
+            col[p] = R[e];
+        }
+    }
+    free(R); free(C);
+    /* sort + dedup every row in place; cursor[i] becomes the row's final length */
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t *a = col + start[i];
+        const int64_t len = start[i + 1] - start[i];
+        if (len > 24) qsort(a, (size_t)len, 4, cmp_u32);
+        else for (int64_t x = 1; x < len; x++) { uint32_t v = a[x]; int64_t y = x; while (y > 0 && a[y - 1] > v) { a[y] = a[y - 1]; y--; } a[y] = v; }
+        int64_t m = 0;
+        for (int64_t x = 0; x < len; x++) if (x == 0 || a[x] != a[x - 1]) a[m++] = a[x];
+        cursor[i] = m;
+    }
+    int64_t *Ap = (int64_t *)malloc((size_t)(n + 1) * 8);
+    if (!Ap) { free(col); free(start); free(cursor); return -2; }
+    Ap[0] = 0;
+    for (int64_t i = 0; i < n; i++) Ap[i + 1] = Ap[i] + cursor[i];
+    const int64_t nnz = Ap[n];
+    int64_t *Aj = (int64_t *)malloc((size_t)(nnz > 0 ? nnz : 1) * 8);
+    if (!Aj) { free(col); free(start); free(cursor); free(Ap); return -2; }
+#pragma omp parallel for schedule(dynamic, 1024)
+    for (int64_t i = 0; i < n; i++) {
+        const uint32_t *a = col + start[i];
+        int64_t *o = Aj + Ap[i];
+        for (int64_t x = 0; x < cursor[i]; x++) o[x] = a[x];
+    }
+    free(col); free(start); free(cursor);
+    *Ap_out = Ap; *Aj_out = Aj; *nnz_out = nnz;
+    return 0;
+}
+/* per-entry values of oracle.py:edge_value for a CSR: the value belongs to the EDGE (src, dst); by_col = 1 when the CSR
+ * rows are destinations (the transposed layout above).  mode 1: integer weight in [1,255]; mode 2: float in (0,1]. */
+int orc_csr_edge_values(int tcode, int mode, int by_col, int64_t nrows, const int64_t *Ap, const int64_t *Aj, void *out) {
+    if (tcode != T_FP32 && tcode != T_FP64 && tcode != T_INT64 && tcode != T_INT32 && tcode != T_UINT32) return -1;
+#pragma omp parallel for schedule(dynamic, 1024)
+    for (int64_t i = 0; i < nrows; i++)
+        for (int64_t p = Ap[i]; p < Ap[i + 1]; p++) {
+            const uint64_t src = by_col ? (uint64_t)Aj[p] : (uint64_t)i, dst = by_col ? (uint64_t)i : (uint64_t)Aj[p];
+            uint64_t h = (src * 0x9E3779B97F4A7C15ull) ^ (dst * 0xC2B2AE3D27D4EB4Full);
+            h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+            if (mode == 1) {
+                const uint64_t w = 1 + h % 255;
+                if (tcode == T_INT64) ((int64_t *)out)[p] = (int64_t)w;
+                else if (tcode == T_INT32) ((int32_t *)out)[p] = (int32_t)w;
+                else if (tcode == T_UINT32) ((uint32_t *)out)[p] = (uint32_t)w;
+                else if (tcode == T_FP32) ((float *)out)[p] = (float)w;
+                else ((double *)out)[p] = (double)w;
+            } else {
+                const double x = (double)(h >> 40) + 1.0;
+                if (tcode == T_FP32) ((float *)out)[p] = (float)x / 16777216.0f;
+                else if (tcode == T_FP64) ((double *)out)[p] = x / 16777216.0;
+                else if (tcode == T_INT64) ((int64_t *)out)[p] = 0;
+                else if (tcode == T_INT32) ((int32_t *)out)[p] = 0;
+                else ((uint32_t *)out)[p] = 0;
+            }
+        }
+    return 0;
+}

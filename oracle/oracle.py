@@ -239,8 +239,11 @@ def _take_csr(nrows, ncols, Cp, Cj, Cx, dt):
     nnz = int(indptr[-1])
     indices = np.ctypeslib.as_array(Cj, shape=(max(nnz, 1),))[:nnz].copy()
     nb = np.dtype(NP_TYPES[dt]).itemsize
-    raw = ctypes.string_at(Cx, nnz * nb) if nnz else b""
-    values = np.frombuffer(raw, dtype=NP_TYPES[dt]).copy()
+    if nnz:      # (ctypes.string_at takes a C int: results beyond 2 GB, e.g. the scale-17 SpGEMM, need the array route)
+        raw = np.ctypeslib.as_array(ctypes.cast(Cx, ctypes.POINTER(ctypes.c_ubyte)), shape=(nnz * nb,))
+        values = raw.view(NP_TYPES[dt]).copy()
+    else:
+        values = np.zeros(0, dtype=NP_TYPES[dt])
     L.orc_free(Cp), L.orc_free(Cj), L.orc_free(Cx)
     return Mat(indptr, indices, values, (nrows, ncols), dt)
 
@@ -391,6 +394,36 @@ def rmat_pattern(scale, edgefactor=16, seed=None, symmetrize=False):
         keys = np.concatenate([keys, dst * n + src])
     keys = np.unique(keys)
     return (keys // n).astype(np.int64), (keys % n).astype(np.int64)
+
+
+def set_num_threads(n):
+    """OpenMP threads of the C restatement (bench.py's CPU arm: torchrun exports OMP_NUM_THREADS=1)."""
+    lib().orc_set_num_threads(int(n))
+
+
+def rmat_csr(scale, dtype, edgefactor=16, seed=None, symmetrize=False, value_mode=0, transpose=False):
+    """rmat_matrix(...) (transpose=False) or its transpose, built by the parallel C path: the same Mat, bit for bit, as
+    the numpy path above (tests/test_oracle_golden.py), at the sizes bench.py's CPU arm needs (scale 23-26)."""
+    L = lib()
+    seed = 42 + scale if seed is None else seed
+    n = 1 << scale
+    Ap, Aj, nnz = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int64()
+    rc = L.orc_rmat_csr(int(scale), ctypes.c_uint64(edgefactor << scale), ctypes.c_uint64(seed), int(transpose),
+                        int(symmetrize), ctypes.byref(Ap), ctypes.byref(Aj), ctypes.byref(nnz))
+    assert rc == 0, f"orc_rmat_csr failed ({rc})"
+    nnz = nnz.value
+    indptr = np.ctypeslib.as_array(ctypes.cast(Ap, ctypes.POINTER(ctypes.c_int64)), shape=(n + 1,)).copy()
+    indices = np.ctypeslib.as_array(ctypes.cast(Aj, ctypes.POINTER(ctypes.c_int64)), shape=(max(nnz, 1),))[:nnz].copy()
+    L.orc_free(Ap)
+    L.orc_free(Aj)
+    if value_mode == 0:
+        vals = np.ones(nnz, dtype=NP_TYPES[dtype])
+    else:
+        vals = np.empty(nnz, dtype=NP_TYPES[dtype])
+        rc = L.orc_csr_edge_values(TYPE_CODES[dtype], int(value_mode), int(transpose), ctypes.c_int64(n), _p(indptr),
+                                   _p(indices), _p(vals))
+        assert rc == 0, f"orc_csr_edge_values: unsupported type {dtype}"
+    return Mat(indptr, indices, vals, (n, n), dtype)
 
 
 def edge_value(rows, cols, mode, dtype):

@@ -158,6 +158,38 @@ def test_assign_index_list(gb, dt):
         w[[n + 3]] << 1
 
 
+@pytest.mark.parametrize("dt", ["UINT32", "INT64", "INT32"])
+@pytest.mark.parametrize("acc", ["min", "max", "plus"])
+def test_assign_duplicate_indices_fold_under_the_accumulator(gb, dt, acc):
+    """`f(binary.min)[I] << mngp` with DUPLICATE indices: FastSV's hooking step (reference notebooks/Connected Components --
+    FastSV.ipynb cell 30) relies on every duplicate being folded with the accumulator (SuiteSparse does; the C API leaves it
+    undefined).  k_assign_atomic against a numpy restatement (ufunc.at), bit-exact on integers, heavy duplication."""
+    from graphblas_b200 import binary
+
+    rng = np.random.default_rng(21)
+    n, ni = 2000, 9000                        # 4.5 writes per target on average, some targets untouched
+    wv, wp = _rand(rng, n, dt, 0.7)
+    uv, up = _rand(rng, ni, dt, 0.8)
+    I = rng.integers(0, n // 2, size=ni)      # only the lower half is hit
+    w, u = _vec(gb, wv, wp, dt), _vec(gb, uv, up, dt)
+    w(getattr(binary, acc))[I] << u
+    ufunc = {"min": np.minimum, "max": np.maximum, "plus": np.add}[acc]
+    tgt, src = I[up], uv[up]
+    ref_v, ref_p = wv.copy(), wp.copy()
+    fresh = ~wp
+    if acc == "plus":
+        ref_v[fresh] = 0
+    else:
+        info = np.iinfo(ref_v.dtype)
+        ref_v[fresh] = info.max if acc == "min" else info.min       # identity where w had no entry
+    ufunc.at(ref_v, tgt, src)
+    ref_p[tgt] = True
+    gv, gp = w.to_dense()
+    assert np.array_equal(gp.astype(bool), ref_p)
+    assert np.array_equal(gv[ref_p], ref_v[ref_p])
+    assert w.nvals == int(ref_p.sum())
+
+
 @pytest.mark.parametrize("dt,mon", [("INT64", "plus"), ("FP32", "plus"), ("INT32", "min"), ("UINT32", "max"), ("BOOL", "lor"),
                                     ("BOOL", "land")])
 def test_reduce_rowwise_columnwise(gb, dt, mon):

@@ -151,7 +151,8 @@ def test_fastsv_vs_scipy_and_permutation(gb):
     assert np.array_equal(vals[a] == vals[b], vp[p[a]] == vp[p[b]])
 
 
-# ---- BASELINE's full sizes, through size-independent properties (the oracle does not finish these in seconds) ----
+# ---- BASELINE's full sizes through size-independent properties; oracle-vs-CUDA parity on the same graphs at scale 16-18
+# (SpGEMM, whole CSR), 20 (triangle counting), 22 (Bellman-Ford) and 18 (BFS) is tests/test_gpu_baseline_parity.py ----
 @pytest.mark.parametrize("scale,dt", [(18, "INT64"), (20, "FP64")])
 def test_spgemm_full_size_row_sums(gb, scale, dt):
     """(A A) 1 = A (A 1): the row sums of C = A.mxm(A, plus_times) against two mxv's of the ones vector.  INT64 wraps
@@ -197,4 +198,7 @@ def test_triangle_count_scale20_two_algorithms(gb):
             gb.set_option("dot_hash", 1)
     assert out[0].nvals == out[1].nvals
     assert out[0].isequal(out[1])
-    assert int(out[0].reduce_scalar(monoid.plus).value) == 423274849      # same count as every earlier run of this graph
+    # the count, pattern and values themselves are checked against the CPU oracle's masked dot product in
+    # tests/test_gpu_baseline_parity.py::test_triangle_count_scale20_pattern_values_and_count; here the two device paths only
+    # have to agree with each other (both alike wrong would be caught there)
+    assert int(out[0].reduce_scalar(monoid.plus).value) == int(out[1].reduce_scalar(monoid.plus).value)

@@ -470,6 +470,34 @@ GrB_Info GxB_b200_Matrix_rmat(GrB_Matrix *A, GrB_Type type, int scale, int edgef
                               int symmetrize, int value_mode);
 GrB_Info GxB_b200_rmat_edges_host(uint64_t *src, uint64_t *dst, int scale, uint64_t nedges, uint64_t seed);
 GrB_Info GxB_b200_Matrix_rowblock(GrB_Matrix *C, const GrB_Matrix A, GrB_Index row_begin, GrB_Index row_end);
+/* multi-GPU exchange over NVLink peer memory (csrc/grb_peer.cu; no reference counterpart: python-graphblas is single-process).
+ * Vector_wrap_device: a full vector over caller-owned device memory (a symmetric buffer the peers map), so a product's
+ *   partial sums land where the other GPUs can read them.
+ * peer_reduce_scatter_FP32: out[i] = sum over ranks q of ((float *)(peer_bases[q] + data_offset_bytes))[i], i < count, after a
+ *   flag handshake with every peer (flag group of `world` uint32 at flag_offset_bytes in every buffer, value seq, compared
+ *   modulo 2^32); uses multimem.ld_reduce through multicast_base when it is non-zero; optionally out_scaled = out / div and,
+ *   afterwards, fill[0 .. fill_count) = fill_value (the other generation of the local partial-sum buffer: once every rank has
+ *   reported for iteration k nobody reads generation k - 1 any more).  ctas < 0: |ctas| small CTAs that fit beside a product.
+ *   peer_bases is a HOST array of `world` device addresses.  Runs on `stream`, beside the next chunk's product. */
+GrB_Info GxB_b200_Vector_wrap_device(GrB_Vector *v, GrB_Type type, GrB_Index n, void *values);
+GrB_Info GxB_b200_peer_reduce_scatter_FP32(float *out, float *out_scaled, const float *div, const uint64_t *peer_bases,
+                                           uint64_t multicast_base, uint64_t data_offset_bytes, uint64_t count,
+                                           uint64_t flag_offset_bytes, int world, int rank, uint32_t seq,
+                                           float *fill, uint64_t fill_count, float fill_value, int ctas, void *stream);
+/* the fused form: GxB_b200_next_product_progress makes the NEXT unmasked pull product count finished tiles per row block
+ * (counters: uint64[nblocks + 2] in device memory, monotonic, the last two words receive debug time stamps; expected[b] receives the tiles touching block b);
+ * GxB_b200_peer_exchange_fused_FP32 runs beside that product on another stream: it announces every block to its owner as
+ * soon as the local product has passed it, waits for all ranks' announcements about this rank's block, sums the N copies
+ * (as peer_reduce_scatter) and optionally refills `fill[fill_count]` with fill_value (the generation of the partial-sum
+ * buffer the product after next accumulates into).  product_seq = how many products have reported into `counters` so far,
+ * this one included. */
+GrB_Info GxB_b200_next_product_progress(uint64_t *counters, uint64_t *expected, int nblocks, GrB_Index rows_per_block);
+GrB_Info GxB_b200_peer_debug_stamps(uint64_t *out8);   /* phase stamps (ns) of the last fused exchange: start, first/last announce, flags, reduce, refill */
+GrB_Info GxB_b200_peer_exchange_fused_FP32(float *out, float *out_scaled, const float *div, const uint64_t *peer_bases,
+                                           uint64_t multicast_base, uint64_t data_offset_bytes, uint64_t count,
+                                           uint64_t flag_offset_bytes, int world, int rank, uint32_t seq,
+                                           const uint64_t *progress, const uint64_t *expected, uint64_t product_seq,
+                                           float *fill, uint64_t fill_count, float fill_value, int ctas, void *stream);
 
 /* ---- allocation-free product.  No counterpart in the reference: added at the request of the run's operators for callers
  *      that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
