@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
     ap.add_argument("--spgemm-scale", type=int, default=20)
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
+    ap.add_argument("--no-legs", action="store_true", help="skip the bounded legs of BASELINE configs[0], [2], [3] (bfs / sssp / tc keys)")
+    ap.add_argument("--sssp-scale", type=int, default=24)
+    ap.add_argument("--tc-scale", type=int, default=22)
     return ap.parse_args()
 
 
@@ -283,7 +286,7 @@ def workload_config(scale, nnz, gpus):
     return {"workload": f"PageRank x{ITERS} iterations: r(plus) << A.T.mxv(w, plus_times) FP32, R-MAT scale {scale} "
                         f"edgefactor 16 (BASELINE configs[1]; weak scaling: scale 22 + log2(gpus))",
             "scale": scale, "nnz": int(nnz), "iterations": ITERS,
-            "parallelism": "1 GPU" if gpus == 1 else f"1-D row blocks over {gpus} GPUs + NCCL all-gather of w",
+            "parallelism": "1 GPU" if gpus == 1 else f"{gpus} GPUs: 1-D partition of the pull matrix, one exchange of vector blocks per iteration",
             "l2": "inputs larger than L2 (matrix stream >= 0.8 GB per iteration vs 126 MB L2); no explicit flush"}
 
 
@@ -1045,11 +1048,11 @@ def run_b200(args):
             pass
     line["clocks"] = clk.summary()
     if world > 1:
-        line["config"]["partition"] = job.partition
-        line["config"]["chunks"] = job.chunks
+        # (the reference arm prints the same `config`; how THIS arm shards the job is described under "sharding")
+        line["sharding"] = {"partition": job.partition, "chunks": job.chunks}
         if job.partition == "fused":
             how = "multimem.ld_reduce through the NVSwitch multicast address" if job.multicast else "P2P loads"
-            line["config"]["parallelism"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local); partial sums for all n "
+            line["sharding"]["how"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local); partial sums for all n "
                                              f"rows accumulate in NVLink peer memory; one exchange kernel per product runs BESIDE it, ships each "
                                              f"rank's rows when the product has passed them, sums the {world} copies ({how}), writes r_p and the "
                                              f"next w_p and refills the buffer: no NCCL call in the loop")
@@ -1069,7 +1072,7 @@ def run_b200(args):
                                   "avg_us_resident": (x_ms / x_cnt * 1e3) if x_cnt else None,
                                   "note": "resident time includes waiting for the product it runs beside", "nccl_calls_in_timed_region": 0}
         elif job.partition == "peer":
-            line["config"]["parallelism"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local), partial sums for all n "
+            line["sharding"]["how"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local), partial sums for all n "
                                              f"rows in NVLink peer memory, summed per row chunk ({job.chunks} chunks) by the library's exchange kernel "
                                              f"({'multimem.ld_reduce through the NVSwitch multicast address' if job.multicast else 'P2P loads'}) beside the next chunk's product")
             x_ms, x_cnt = 0.0, 0
@@ -1078,7 +1081,7 @@ def run_b200(args):
                                   "bytes_received_per_rank_per_iteration": int((job.hi - job.lo) * 4 * (1 if job.multicast else world - 1)),
                                   "nccl_calls_in_timed_region": 0}
         elif job.partition == "col":
-            line["config"]["parallelism"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local), partial sums for all n "
+            line["sharding"]["how"] = (f"1-D column blocks of the pull matrix over {world} GPUs (w_p = r_p / d_p local), partial sums for all n "
                                              f"rows, NCCL reduce-scatter(sum) in {job.chunks} row chunks pipelined behind the products")
             line["collective"] = {"name": "ncclReduceScatter(sum, f32)", "calls_per_iteration": job.chunks,
                                   "bytes_in_per_rank_per_iteration": int(job.n * 4), "bytes_out_per_rank_per_iteration": int((job.hi - job.lo) * 4)}
@@ -1100,12 +1103,32 @@ def run_b200(args):
         e2e = None if args.no_e2e else measure_e2e_sharded(gb, job, args)      # collective: every rank takes part
         if rank == 0:
             line["e2e"] = e2e
+    legs = not args.no_legs
     if rank == 0 and world == 1 and not args.no_spgemm:
         del job
         try:
             line["spgemm"] = measure_spgemm(gb, args.spgemm_scale)
         except Exception as exc:                 # the contract line must survive a failure of the second leg
             line["spgemm"] = {"error": f"{type(exc).__name__}: {exc}"}
+    if world == 1 and rank == 0 and legs:
+        # the other BASELINE configs, bounded, as extra keys of the same line (the headline stays PageRank)
+        job = None
+        for key, fn in (("bfs", lambda: measure_bfs(gb)), ("sssp", lambda: measure_sssp(gb, args.sssp_scale, 0, 1)),
+                        ("tc", lambda: measure_tc(gb, args.tc_scale))):
+            try:
+                line[key] = fn()
+            except Exception as exc:
+                line[key] = {"error": f"{type(exc).__name__}: {exc}"}
+    elif world > 1 and legs:
+        # configs[2] as stated: SSSP scale 24 row-sharded over the N GPUs (strong scaling), every rank takes part
+        job = None
+        torch.cuda.empty_cache()
+        try:
+            leg = measure_sssp(gb, args.sssp_scale, rank, world)
+        except Exception as exc:
+            leg = {"error": f"{type(exc).__name__}: {exc}"}
+        if rank == 0:
+            line["sssp"] = leg
     if rank == 0 and world == 1 and args.extra:
         if args.breakdown:
             gb.lib.GxB_b200_kernel_time_reset()
@@ -1366,6 +1389,191 @@ def measure_spgemm(gb, scale, reps=2):
                          "algorithmic_bytes": int(alg), "peak_source": peak_src,
                          "numeric_heavy_rows_ms": (k_ms / k_cnt) if k_cnt else None,
                          "symbolic_heavy_rows_ms": (s_ms / s_cnt) if s_cnt else None}}
+
+
+# ---------------------------------------------------------------------------------------------- bounded legs of the other configs
+def measure_bfs(gb, scale=18, reps=5):
+    """BASELINE configs[0]: level BFS `q(~v.S, replace=True) << q.vxm(A, any_pair)` on the symmetrised R-MAT scale-18 graph
+    (the reference's CPU-runnable case) from the highest-degree vertex: device time of one traversal, TEPS by the Graph500
+    convention (edges of the traversed component / time), the CPU port on the same graph beside it, and bit-exact parity of
+    the level vector."""
+    import torch
+    from graphblas_b200 import Matrix, workloads as W
+    from oracle import oracle as O
+
+    A = Matrix.rmat(scale, "BOOL", symmetrize=True)
+    n = 1 << scale
+    rp = gb.ffi.new("void**")
+    gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
+    rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+    deg = (rowptr[1:] - rowptr[:-1])
+    src = int(torch.argmax(deg).item())
+    W.bfs_levels(A, src)                                   # warm-up: cached transpose
+    times = []
+    l0 = gb.launch_count()
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        v, st = W.bfs_levels(A, src)
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1))
+    launches = (gb.launch_count() - l0) // reps
+    vals, pres = v.to_dense()
+    pres = pres.astype(bool)
+    edges = int(deg.cpu().numpy()[pres].sum())
+    ms = float(np.median(times))
+    out = {"workload": f"level BFS any_pair masked vxm, symmetrised R-MAT scale {scale} (BASELINE configs[0])", "ms": ms, "ms_best": min(times),
+           "levels": st["levels"], "frontier_sizes": st["frontier_sizes"], "reached": int(pres.sum()), "edges_traversed": edges,
+           "value": edges / ms / 1e6, "unit": "GTEPS (edges of the traversed component / time)", "nnz": A.nvals, "gpu_launches": int(launches),
+           "bound": "launch latency: 6 levels x (assign + vxm) of a 0.26 M-vertex graph; no HBM roofline applies"}
+    # CPU port on the same graph + parity of the levels
+    O.build()
+    O.set_num_threads(host_threads())
+    H = O.rmat_csr(scale, "BOOL", symmetrize=True)
+
+    def cpu_bfs():
+        lv = O.Vec.empty(n, "INT32")
+        q = O.Vec.from_coo([src], [True], n, "BOOL")
+        level = 0
+        while q.nvals:
+            level += 1
+            m = q.present.astype(bool)
+            lv.values[m] = level
+            lv.present[m] = 1
+            nq = O.Vec.empty(n, "BOOL")
+            O.vxm(nq, q, H, "ANY", "PAIR", "BOOL", mask=lv, comp=True, structure=True, replace=True, At=H)
+            q = nq
+        return lv
+
+    lv = cpu_bfs()
+    t0, done = time.perf_counter(), 0
+    while done < 3 or time.perf_counter() - t0 < 3.0:
+        cpu_bfs()
+        done += 1
+    dt = (time.perf_counter() - t0) / done
+    p = lv.present.astype(bool)
+    out["parity_bit_exact"] = bool(np.array_equal(p, pres) and np.array_equal(lv.values[p], vals[p]))
+    out["cpu_baseline"] = {"value": edges / dt / 1e9, "unit": "GTEPS", "ms": dt * 1e3, "cores": O.num_threads(), "kind": "port",
+                           "sample": f"{done} traversals of the same graph from the same source (pull with mask early-out per level)"}
+    return out
+
+
+def measure_tc(gb, scale=22, reps=2):
+    """BASELINE configs[3]: `C(L.S) << L.mxm(L.T, plus_pair)` + reduce on the symmetrised R-MAT scale-22 graph.  Algorithmic bytes
+    (SURVEY 8d): nnz(M)*2I + sum over mask entries (deg i + deg j)*I + nnz(C)*(I + 8)."""
+    import torch
+    from graphblas_b200 import Matrix, monoid, semiring
+
+    G = Matrix.rmat(scale, "INT64", symmetrize=True)
+    L = G.select("tril", -1).new()
+    del G
+    n = 1 << scale
+    rp, ci = gb.ffi.new("void**"), gb.ffi.new("void**")
+    gb.lib.GxB_b200_Matrix_device_ptrs(rp, ci, gb.ffi.NULL, L._carg)
+    nnz_l = L.nvals
+    rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+    col = dev_tensor(int(gb.ffi.cast("uintptr_t", ci[0])), nnz_l, "<i4").to(torch.int64)
+    deg = (rowptr[1:] - rowptr[:-1])
+    pair_len = int((deg * deg).sum().item()) + int(deg[col].sum().item())      # sum over mask entries of deg(i) + deg(j)
+    del col
+
+    def product():
+        C = Matrix("INT64", n, n)
+        C(L.S) << L.mxm(L.T, semiring.plus_pair)
+        return int(C.reduce_scalar(monoid.plus).value or 0), C.nvals
+
+    product()
+    gb.lib.GxB_b200_kernel_time_reset()
+    gb.set_option("timing", 1)
+    times = []
+    l0 = gb.launch_count()
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ntri, nnz_c = product()
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1))
+    launches = (gb.launch_count() - l0) // reps
+    gb.set_option("timing", 0)
+    k_ms, k_cnt = kernel_time(gb, "dot_masked")
+    ms = sum(times) / len(times)
+    alg = nnz_l * 8 + pair_len * 4 + nnz_c * 12
+    peak, peak_src = measured_peaks()
+    k = (k_ms / k_cnt) if k_cnt else None
+    return {"workload": f"C(L.S) << L.mxm(L.T, plus_pair) + reduce, L = tril of the symmetrised R-MAT scale {scale} graph (BASELINE configs[3])",
+            "value": nnz_l / ms * 1e3, "unit": "mask entries/s", "ms": ms, "ms_best": min(times), "nnz_L": nnz_l, "nnz_C": nnz_c, "triangles": ntri,
+            "triangles_per_s": ntri / ms * 1e3, "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_dot_masked<plus_pair,int64>", "achieved": (alg / k / 1e6) if k else None, "peak": peak,
+                         "unit": "GB/s", "frac": (alg / k / 1e6 / peak) if k else None, "traffic": None, "algorithmic_bytes": int(alg),
+                         "avg_launch_ms": k, "kernel_share_of_step": (k / ms) if k else None, "peak_source": peak_src,
+                         "note": "algorithmic bytes count both rows of every mask entry in full (sorted-merge formulation, SURVEY 8d); the kernel probes "
+                                 "per-row hash sets with the shorter row only"}}
+
+
+def measure_sssp(gb, scale, rank, world, steps=3):
+    """BASELINE configs[2]: Bellman-Ford `w(min) << w.vxm(A, min_plus)` INT64 to the fixed point on the symmetrised R-MAT graph of
+    `scale`, output rows sharded over `world` GPUs (strong scaling).  Returns the leg's dict on rank 0, None elsewhere."""
+    import torch
+    import torch.distributed as dist
+
+    job = SsspJob(gb, scale, rank, world, "sssp")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        job.step()
+    barrier()
+    gb.lib.GxB_b200_kernel_time_reset()
+    gb.set_option("timing", 1)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = gb.launch_count()
+    ev0.record()
+    for _ in range(steps):
+        job.step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = gb.launch_count() - l0
+    gb.set_option("timing", 0)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    if world == 1:
+        vals, pres = job.w.to_dense()
+        reached, checksum = int(pres.sum()), int(vals[pres.astype(bool)].sum())
+    else:
+        bv, bp = job._tensors(job.wb, job.hi - job.lo)
+        part = torch.stack([bp.to(torch.int64).sum(), (bv.to(torch.int64) * bp.to(torch.int64)).sum()])
+        dist.all_reduce(part)
+        reached, checksum = int(part[0].item()), int(part[1].item())
+    nnz, iters = job.nnz_total, job.iterations
+    k_ms, k_cnt = kernel_time(gb, "spmv_red")
+    k2_ms, k2_cnt = kernel_time(gb, "spmv_red_sparse")
+    k_ms, k_cnt = k_ms + k2_ms, k_cnt + k2_cnt
+    products = steps * iters
+    k_per_product = k_ms / max(products, 1)
+    peak, peak_src = measured_peaks()
+    alg = job.nnz_local * (4 + 8 + 8) + (job.hi - job.lo) * (8 + 2 * 8)
+    out = {"workload": f"Bellman-Ford SSSP to the fixed point: w(min) << w.vxm(A, min_plus) INT64, symmetrised R-MAT scale {scale} "
+                       f"(BASELINE configs[2]), output rows sharded over {world} GPU(s); TEPS = iterations x nnz / time",
+           "value": steps * iters * nnz / ms / 1e6, "unit": "GTEPS", "ms_per_run": ms / steps, "iterations": iters, "nnz": nnz, "n_gpus": world,
+           "scaling": "strong", "reached": reached, "distance_checksum": checksum, "gpu_launches": int(launches // steps),
+           "roofline": {"bound": "hbm", "kernel": "k_spmv_red<min_plus,int64> (full and sparse-vector variants)",
+                        "achieved": (alg / k_per_product / 1e6) if k_cnt else None, "peak": peak, "unit": "GB/s",
+                        "frac": (alg / k_per_product / 1e6 / peak) if k_cnt else None, "traffic": None,
+                        "algorithmic_bytes_per_product": int(alg), "ms_per_product": k_per_product if k_cnt else None,
+                        "launches_per_product": k_cnt / max(products, 1), "kernel_share_of_step": (k_ms / ms) if ms else None,
+                        "peak_source": peak_src}}
+    del job
+    return out if rank == 0 else None
 
 
 # ---------------------------------------------------------------------------------------------- configs[3], [4]: sharded mxm

@@ -43,6 +43,7 @@ from grb_b200.errors import (  # noqa: E402,F401
 from . import dtypes  # noqa: E402
 from .operators import binary, monoid, semiring, unary  # noqa: E402
 from .core import Matrix, Scalar, TransposedMatrix, Vector, replace  # noqa: E402
+from . import io  # noqa: E402,F401  (from_scipy_sparse / to_scipy_sparse, reference graphblas/io/_scipy.py)
 
 
 def use_torch_stream():

@@ -298,3 +298,39 @@ def test_rowblock_shards_reassemble(gb):
     ar, ac, av = A.to_coo()
     assert np.array_equal(np.concatenate(rows), ar) and np.array_equal(np.concatenate(cols), ac)
     assert np.array_equal(np.concatenate(vals), av)
+
+
+@pytest.mark.parametrize("fmt", ["csr", "csc", "coo", "lil"])
+def test_from_scipy_sparse_as_in_reference(gb, fmt):
+    """io.from_scipy_sparse / to_scipy_sparse (reference graphblas/io/_scipy.py:8-119): every scipy format lands as the same
+    matrix, unsorted column indices included, duplicates of a COO input folded by dup_op; the product of the ingested matrix
+    equals scipy's."""
+    import scipy.sparse as sp
+    from graphblas_b200 import binary, io, semiring
+
+    rng = np.random.default_rng(17)
+    S = sp.random(300, 200, density=0.05, random_state=3, format="csr", dtype=np.float64)
+    S.data = np.round(S.data * 100) + 1
+    A = io.from_scipy_sparse(S.asformat(fmt))
+    assert A.nvals == S.nnz and (A.nrows, A.ncols) == S.shape
+    back = io.to_scipy_sparse(A, "csr")
+    assert (back != S).nnz == 0
+    x = rng.integers(0, 5, size=200).astype(np.float64)
+    w = A.mxv(gb.Vector.from_dense(x), semiring.plus_times).new()
+    vals, pres = w.to_dense()
+    ref = S @ x
+    has = np.diff(S.indptr) > 0
+    assert np.array_equal(pres.astype(bool), has) and np.array_equal(vals[has], ref[has])
+    if fmt == "coo":                      # duplicates: summed by dup_op, as the reference's from_coo does
+        C = S.tocoo()
+        D = sp.coo_array((np.concatenate([C.data, C.data]), (np.concatenate([C.row, C.row]), np.concatenate([C.col, C.col]))), shape=S.shape)
+        A2 = io.from_scipy_sparse(D, dup_op=binary.plus)
+        assert (io.to_scipy_sparse(A2) != 2 * S).nnz == 0
+    if fmt == "csr":                      # unsorted indices inside rows
+        U = S.copy()
+        for i in range(U.shape[0]):
+            s_, e_ = U.indptr[i], U.indptr[i + 1]
+            o = rng.permutation(e_ - s_)
+            U.indices[s_:e_], U.data[s_:e_] = U.indices[s_:e_][o], U.data[s_:e_][o]
+        U.has_sorted_indices = False
+        assert (io.to_scipy_sparse(io.from_scipy_sparse(U)) != S).nnz == 0

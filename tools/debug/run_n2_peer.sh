@@ -1,14 +1,14 @@
 N=${N:-2}
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-run() { name=$1; shift; timeout -k 5 170 $T bench.py --gpus $N --steps 5 --warmup 3 $( [ -n "$E2E" ] || echo --no-e2e ) --breakdown "$@" > gpurun_out/r02t_n${N}_$name.json 2> gpurun_out/r02t_n${N}_$name.err; python - <<PY
+run() { name=$1; shift; timeout -k 5 170 $T bench.py --gpus $N --steps 5 --warmup 3 $( [ -n "$E2E" ] || echo --no-e2e ) --breakdown --no-legs "$@" > gpurun_out/r02v_n${N}_$name.json 2> gpurun_out/r02v_n${N}_$name.err; python - <<PY
 import json
 try:
-    s=[l for l in open("gpurun_out/r02t_n${N}_$name.json") if l.startswith("{")][-1]
+    s=[l for l in open("gpurun_out/r02v_n${N}_$name.json") if l.startswith("{")][-1]
     d=json.loads(s)
     print("N=$N $name", round(d["value"],1), "GTEPS", round(d["ms_per_step"]/20*1000,1), "us/iter  red launch", round(d["roofline"]["avg_launch_ms"]*1000,1), "us x", d["roofline"]["launches_per_product"], " share", round(d["roofline"]["kernel_share_of_step"],2), d.get("parity_vs_single_gpu"))
 except Exception as e: print("$name failed", e)
 PY
-grep "timing\]" gpurun_out/r02t_n${N}_$name.err | awk '{print "    ", $3, $4, $5, $6, $7, $8, $9}' | head -8
+grep "timing\]" gpurun_out/r02v_n${N}_$name.err | awk '{print "    ", $3, $4, $5, $6, $7, $8, $9}' | head -8
 }
 for v in $VARIANTS; do
   case $v in
