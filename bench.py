@@ -59,7 +59,7 @@ def parse_args():
                          "partition with NCCL reduce-scatter; row = round 1's row blocks + NCCL all-gather of w")
     ap.add_argument("--peer-carveout", type=int, default=-2, help="library option peer_carveout (percent; -1 = driver default)")
     ap.add_argument("--peer-ctas", type=int, default=0, help="CTAs of the peer exchange kernel (0 = 148 fused / 296 peer)")
-    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "spgemm", "tc"],
+    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "fastsv", "spgemm", "tc"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
@@ -1164,6 +1164,7 @@ class SsspJob:
 
         self.gb, self.rank, self.world, self.n, self.kind = gb, rank, world, 1 << scale, kind
         n = self.n
+        self.kind = kind
         if kind == "sssp":
             A = Matrix.rmat(scale, "INT64", symmetrize=True, value_mode=1)     # same graph on every rank
             self.dtype, self.typestr, self.vsize = "INT64", "<i8", 8
@@ -1191,7 +1192,7 @@ class SsspJob:
             self.flag = torch.zeros(1, dtype=torch.int32, device="cuda")
         self.nnz_local = (self.P if world > 1 else self.A).nvals
         self.iterations = 0
-        if kind == "cc":                       # initial labels stay on the device; a step starts from copies of them
+        if kind in ("cc", "fastsv"):           # initial labels stay on the device; a step starts from copies of them
             self.f0 = Vector.from_dense(np.arange(n, dtype=np.uint32))
             self.f0b = Vector.from_dense(np.arange(self.lo, self.hi, dtype=np.uint32))
         gb.sync()
@@ -1211,9 +1212,14 @@ class SsspJob:
         if self.world == 1:
             from graphblas_b200 import workloads as W
 
-            self.w, st = W.sssp_bellman_ford(self.A, self.source) if self.kind == "sssp" else W.cc_min_label(self.A, f0=self.f0)
+            if self.kind == "fastsv":
+                self.w, st = W.fastsv(self.A, device_indices=True, f0=self.f0)
+            else:
+                self.w, st = W.sssp_bellman_ford(self.A, self.source) if self.kind == "sssp" else W.cc_min_label(self.A, f0=self.f0)
             self.iterations = st["iterations"]
             return
+        if self.kind == "fastsv":
+            return self._fastsv_sharded()
         if self.kind == "sssp":
             w = Vector("INT64", n)
             w[self.source] = 0
@@ -1241,6 +1247,50 @@ class SsspJob:
                 self.ex.all_gather(wp, bp)
                 gb.lib.GxB_b200_Vector_set_dense_nvals(w._carg, -1)
         self.w, self.wb, self.iterations = w, wb, iters
+
+
+def _fastsv_sharded(self):
+    """FastSV as the reference's notebook writes it (notebooks/Connected Components -- FastSV.ipynb cell 30), sharded: rank p owns
+    the vertices [lo, hi) and their rows of A; f and gp are replicated.  Per iteration: the product `mngp << A.mxv(gp, min_second)`
+    on the rank's rows; its share of the hooking `f(min)[I] << mngp` and `f << min(f, mngp)` applied to its copy of f (I = the
+    parents of its vertices, taken on the device); ONE all-reduce(min) of f merges the shares (every update only lowers f);
+    shortcutting `f << min(f, gp)`, grandparents `gp << f[f]` and the termination test run replicated on the full vectors."""
+    import torch
+    import torch.distributed as dist
+    from graphblas_b200 import Vector, binary, monoid, semiring
+
+    n, lo, hi = self.n, self.lo, self.hi
+    nb = hi - lo
+    f, fb = self.f0.dup(), self.f0b.dup()
+    gp, gp_dup = f.dup(), f.dup()
+    mngp = Vector("UINT32", nb)
+    mod = Vector("BOOL", n)
+    iters, change = 0, True
+    while change:
+        mngp << self.P.mxv(gp, semiring.min_second)
+        f_t, _ = self._tensors(f, n)
+        fb_t, _ = self._tensors(fb, nb)
+        fb_t.copy_(f_t[lo:hi])                          # I = parents of my vertices
+        f(binary.min)[fb] << mngp                       # hooking, duplicates folded with atomicMin
+        f_t, _ = self._tensors(f, n)
+        fb_t.copy_(f_t[lo:hi])
+        fb << fb.ewise_add(mngp, binary.min)            # f[lo:hi] = min(f[lo:hi], mngp)
+        fb_t, _ = self._tensors(fb, nb)
+        f_t[lo:hi].copy_(fb_t)
+        dist.all_reduce(f_t, op=dist.ReduceOp.MIN)      # labels < 2^31: the int32 view orders like uint32
+        f << f.ewise_add(gp, binary.min)                # shortcutting
+        gp << f[f]                                      # grandparents, I = f itself (device index vector)
+        mod << gp_dup.ewise_mult(gp, binary.ne)
+        change = bool(mod.reduce(monoid.lor).value)
+        gp_dup << gp
+        iters += 1
+    self.w, self.wb, self.iterations = f, fb, iters
+    self._full_result = f
+
+
+
+
+SsspJob._fastsv_sharded = _fastsv_sharded
 
 
 def run_sssp(args):
@@ -1296,7 +1346,11 @@ def run_sssp(args):
         vals, pres = job.w.to_dense()
         reached, checksum = int(pres.sum()), int(vals[pres.astype(bool)].sum())
     else:
-        bv, bp = job._tensors(job.wb, job.hi - job.lo)
+        if kind == "fastsv":       # f is replicated: this rank's slice of it
+            fv, fp = job._tensors(job.w, job.n)
+            bv, bp = fv[job.lo:job.hi], fp[job.lo:job.hi]
+        else:
+            bv, bp = job._tensors(job.wb, job.hi - job.lo)
         part = torch.stack([bp.to(torch.int64).sum(), (bv.to(torch.int64) * bp.to(torch.int64)).sum()])
         dist.all_reduce(part)
         reached, checksum = int(part[0].item()), int(part[1].item())
@@ -1318,6 +1372,11 @@ def run_sssp(args):
             "config": {"workload": (f"Bellman-Ford SSSP to the fixed point: w(min) << w.vxm(A, min_plus) INT64, symmetrised R-MAT scale "
                                     f"{args.scale} edgefactor 16 (BASELINE configs[2]), output rows sharded over {world} GPU(s), "
                                     "all-gather of values + presence per iteration; TEPS = iterations x nnz / time") if kind == "sssp" else
+                                   (f"Connected components by FastSV as the reference's notebook writes it (hooking f(min)[I] << mngp with "
+                                    f"duplicate indices, shortcutting, grandparents gp << f[I]; I = f on the device), UINT32, symmetrised R-MAT scale "
+                                    f"{args.scale} edgefactor 16 (BASELINE configs[4]b), rows of A sharded over {world} GPU(s), f and gp replicated, one "
+                                    "all-reduce(min) of f per iteration; TEPS = iterations x nnz / time; checksum = sum of the component labels, equal "
+                                    "to min-label propagation's (--workload cc)") if kind == "fastsv" else
                                    (f"Connected components by FastSV's product folded into min-label propagation: f(min) << A.mxv(f, min_second) "
                                     f"UINT32 to the fixed point, symmetrised R-MAT scale {args.scale} edgefactor 16 (BASELINE configs[4]b), output "
                                     f"rows sharded over {world} GPU(s), all-gather of the labels per iteration; TEPS = iterations x nnz / time"),
@@ -1752,7 +1811,7 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
-    elif args.workload in ("sssp", "cc"):
+    elif args.workload in ("sssp", "cc", "fastsv"):
         run_sssp(args)
     elif args.workload in ("spgemm", "tc"):
         run_sharded_mxm(args)

@@ -116,8 +116,17 @@ static void check_bad(int *d_bad, const char *what) {
     if (bad) grb_throw(GrB_INDEX_OUT_OF_BOUNDS, std::string(what) + ": index out of bounds");
 }
 
+static void vector_assign_indexed_dev(GB_Object *w, GB_Object *mask, int accum, GB_Object *u, uint64_t *dI, int64_t ni,
+                                      const DescFlags &f);
 void vector_assign_indexed(GB_Object *w, GB_Object *mask, int accum, GB_Object *u, const uint64_t *I, int64_t ni,
                            const DescFlags &f) {
+    need_vec(w, "w"); need_vec(u, "u");
+    if (u->nrows != ni) grb_throw(GrB_DIMENSION_MISMATCH, "assign: u must have one entry slot per index");
+    vector_assign_indexed_dev(w, mask, accum, u, upload_indices(I, ni), ni, f);
+}
+// dI: device index array, consumed (freed) here
+static void vector_assign_indexed_dev(GB_Object *w, GB_Object *mask, int accum, GB_Object *u, uint64_t *dI, int64_t ni,
+                                      const DescFlags &f) {
     need_vec(w, "w"); need_vec(u, "u");
     const int64_t n = w->nrows;
     if (u->nrows != ni) grb_throw(GrB_DIMENSION_MISMATCH, "assign: u must have one entry slot per index");
@@ -130,7 +139,6 @@ void vector_assign_indexed(GB_Object *w, GB_Object *mask, int accum, GB_Object *
         cast_array(u->vals, u->type->code, uc, wcode, ni);
         uv = uc;
     }
-    uint64_t *dI = upload_indices(I, ni);
     void *z = dmalloc((size_t)(n > 0 ? n : 1) * w->type->size);
     uint8_t *zp = dalloc<uint8_t>(n);
     d2d(z, w->vals, (size_t)n * w->type->size);
@@ -211,6 +219,54 @@ GrB_Info GrB_Vector_extract(GrB_Vector w_, const GrB_Vector mask_, const GrB_Bin
     const int64_t ni = (int64_t)ni_;
     if (ni != n) grb_throw(GrB_DIMENSION_MISMATCH, "extract: w must have one entry slot per index");
     uint64_t *dI = upload_indices(I, ni);
+    void *t = dmalloc((size_t)(ni > 0 ? ni : 1) * u->type->size);
+    uint8_t *tp = dalloc<uint8_t>(ni);
+    int *bad = dalloc<int>(1);
+    dzero(bad, sizeof(int));
+    GRB_TYPE_SWITCH(u->type->code, T, {
+        GRB_LAUNCH("extract", k_extract<T>, ew_grid(ni), 256, 0, (const T *)u->vals, u->present, dI, ni, u->nrows, (T *)t, tp, bad);
+    });
+    try { check_bad(bad, "extract"); } catch (...) { dfree(t); dfree(tp); dfree(dI); throw; }
+    vec_writeback_any(w, mask, desc_flags(desc), accum_code_of(accum), t, u->type->code, tp);
+    dfree(t); dfree(tp); dfree(dI);
+    API_END(w_)
+}
+
+// ---- index lists that already live in HBM (the values of a full integer vector), as SuiteSparse's GxB_Vector_assign_Vector /
+// GxB_Vector_extract_Vector take them.  FastSV's `f(min)[I] << mngp` and `gp << f[I]` use I = the parent vector f itself: with
+// the host-array forms the notebook pulls f to the host and pushes it back every iteration (1.3 GB over PCIe per iteration at
+// scale 26); these keep the loop on the device.
+static uint64_t *indices_of_vector(GB_Object *Iv, int64_t ni) {
+    need_vec(Iv, "I");
+    if (Iv->nrows != ni) grb_throw(GrB_DIMENSION_MISMATCH, "index vector and operand sizes differ");
+    if (vec_nvals(Iv) != ni) grb_throw(GrB_INVALID_VALUE, "the index vector must be full");
+    const int c = Iv->type->code;
+    if (c == TC_FP32 || c == TC_FP64 || c == TC_BOOL) grb_throw(GrB_DOMAIN_MISMATCH, "the index vector must have an integer type");
+    uint64_t *d = dalloc<uint64_t>(ni);
+    cast_array(Iv->vals, c, d, TC_UINT64, ni);
+    return d;
+}
+extern "C" GrB_Info GxB_b200_Vector_assign_Vector(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_Vector u_,
+                                       const GrB_Vector I_, const GrB_Descriptor desc) {
+    API_BEGIN
+    require_init();
+    GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u"), *Iv = obj_check(I_, "I");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    need_vec(u, "u");
+    vector_assign_indexed_dev(w, mask, accum_code_of(accum), u, indices_of_vector(Iv, u->nrows), u->nrows, desc_flags(desc));
+    if (g.blocking) stream_sync();
+    API_END(w_)
+}
+extern "C" GrB_Info GxB_b200_Vector_extract_Vector(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_Vector u_,
+                                        const GrB_Vector I_, const GrB_Descriptor desc) {
+    API_BEGIN
+    require_init();
+    GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u"), *Iv = obj_check(I_, "I");
+    GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
+    need_vec(w, "w"); need_vec(u, "u");
+    const int64_t ni = w->nrows;
+    if (mask && mask->nrows != ni) grb_throw(GrB_DIMENSION_MISMATCH, "extract: mask and w sizes differ");
+    uint64_t *dI = indices_of_vector(Iv, ni);
     void *t = dmalloc((size_t)(ni > 0 ? ni : 1) * u->type->size);
     uint8_t *tp = dalloc<uint8_t>(ni);
     int *bad = dalloc<int>(1);

@@ -642,6 +642,8 @@ class Vector(BaseType):
             return _Assigner(Updater(self), key)
         if isinstance(key, (list, tuple, np.ndarray)):
             return _IndexedVector(self, _np_index(key))
+        if isinstance(key, Vector):
+            return _VectorIndexedVector(self, key)
         out = ffi.new(f"{_CTYPE[self.dtype.name]}*")
         info = call(f"GrB_Vector_extractElement_{self.dtype.name}", [out, self, int(key)])
         s = Scalar(self.dtype)
@@ -650,7 +652,7 @@ class Vector(BaseType):
         return _ScalarResult(s)
 
     def __setitem__(self, key, value):
-        if (isinstance(key, slice) and key == slice(None)) or isinstance(key, (list, tuple, np.ndarray)):
+        if (isinstance(key, slice) and key == slice(None)) or isinstance(key, (list, tuple, np.ndarray, Vector)):
             self._assign(key, value, opts={})
         else:
             call(f"GrB_Vector_setElement_{self.dtype.name}", [self, self.dtype.np_type.type(value).item(), int(key)])
@@ -699,8 +701,20 @@ class Vector(BaseType):
         elif isinstance(key, (list, tuple, np.ndarray)):
             keep = _np_index(key)
             I, ni = _buf(keep, "GrB_Index*"), keep.size
+        elif isinstance(key, Vector):
+            # the index list is the value array of a full integer vector that already lives in HBM
+            # (GxB_b200_Vector_assign_Vector, the counterpart of SuiteSparse's GxB_Vector_assign_Vector)
+            comp = structure = False
+            if mask is not None:
+                comp, structure = mask.complement, mask.structure
+            if isinstance(value, Expression):
+                value = value.new()
+            if not isinstance(value, Vector):
+                raise TypeError("w[index vector] << value needs a Vector value")
+            call("GxB_b200_Vector_assign_Vector", [self, mask, accum, value, key, _descriptor(replace_, comp, structure, **opts)])
+            return
         else:
-            raise NotImplementedError("assignment takes w[:] or w[index list]")
+            raise NotImplementedError("assignment takes w[:], w[index list] or w[index vector]")
         comp = structure = False
         if mask is not None:
             comp, structure = mask.complement, mask.structure
@@ -753,6 +767,21 @@ class _IndexedVector(Expression):
     def __init__(self, src, index):
         super().__init__("extract", "GrB_Vector_extract", [src], None, Vector, (index.size,),
                          scalar_args=(_buf(index, "GrB_Index*"), index.size))
+        self._src, self._index = src, index
+
+    def __lshift__(self, value):
+        self._src._assign(self._index, value, opts={})
+
+    def update(self, value):
+        self._src._assign(self._index, value, opts={})
+
+
+class _VectorIndexedVector(Expression):
+    """u[I] with I a full integer Vector in HBM: `w << u[I]` -> GxB_b200_Vector_extract_Vector; `u(accum)[I] << v` ->
+    GxB_b200_Vector_assign_Vector.  No host round trip of the index list (FastSV: I is the parent vector itself)."""
+
+    def __init__(self, src, index):
+        super().__init__("extract", "GxB_b200_Vector_extract_Vector", [src, index], None, Vector, (index.size,))
         self._src, self._index = src, index
 
     def __lshift__(self, value):

@@ -92,20 +92,26 @@ def cc_min_label(A, max_iters=None, f0=None):
     return f, {"iterations": iters}
 
 
-def fastsv(A, max_iters=None):
+def fastsv(A, max_iters=None, device_indices=False, f0=None):
     """Connected components by FastSV, statement for statement the reference's
     notebooks/Connected Components -- FastSV.ipynb cell 30 (hooking through an indexed min-assign with duplicate
-    indices, shortcutting, grandparents by extract).  f[i] = smallest vertex id of i's component."""
+    indices, shortcutting, grandparents by extract).  f[i] = smallest vertex id of i's component.
+    device_indices: the notebook refreshes the index list with `_, I = f.to_coo()` every iteration (f is full, so I is
+    just f's values pulled to the host and pushed back); with True, I is the Vector f itself and stays in HBM
+    (GxB_b200_Vector_assign_Vector / _extract_Vector) -- same statements, same result, no PCIe round trip."""
     n = A.nrows
     I = np.arange(n)
     dt = "UINT32" if n < (1 << 32) else "UINT64"
-    f = Vector.from_coo(I, I.astype(dt.lower()), size=n, dtype=dt)   # the parent of each vertex is the vertex itself
+    # the parent of each vertex is the vertex itself (f0: the labels 0..n-1 already resident in HBM)
+    f = f0.dup() if f0 is not None else Vector.from_coo(I, I.astype(dt.lower()), size=n, dtype=dt)
     gp = f.dup()              # grandparents
     gp_dup = gp.dup()
     mngp = f.dup()            # minimum grandparent of each star vertex
     mod = Vector("BOOL", n)
     change = True
     iters = 0
+    if device_indices:
+        I = f.dup()
     while change and (max_iters is None or iters < max_iters):
         # Step 1: hooking
         mngp << A.mxv(gp, semiring.min_second)
@@ -114,7 +120,10 @@ def fastsv(A, max_iters=None):
         # Step 2: shortcutting
         f << f.ewise_add(gp, binary.min)
         # Step 3: grandparents
-        _, I = f.to_coo()
+        if device_indices:
+            I << f
+        else:
+            _, I = f.to_coo()
         gp << f[I]
         # termination
         mod << gp_dup.ewise_mult(gp, binary.ne)

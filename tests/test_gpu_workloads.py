@@ -202,3 +202,41 @@ def test_triangle_count_scale20_two_algorithms(gb):
     # tests/test_gpu_baseline_parity.py::test_triangle_count_scale20_pattern_values_and_count; here the two device paths only
     # have to agree with each other (both alike wrong would be caught there)
     assert int(out[0].reduce_scalar(monoid.plus).value) == int(out[1].reduce_scalar(monoid.plus).value)
+
+
+def test_fastsv_device_index_vectors_match_the_notebook_form(gb):
+    """FastSV with I kept in HBM (GxB_b200_Vector_assign_Vector / _extract_Vector, I = the parent vector) gives the labels of the
+    notebook's own statements (host index lists) and of scipy's connected_components, iteration count included."""
+    from graphblas_b200 import workloads as W
+
+    A = gb.Matrix.rmat(13, "BOOL", symmetrize=True)
+    f_host, st_host = W.fastsv(A)
+    f_dev, st_dev = W.fastsv(A, device_indices=True)
+    assert st_host["iterations"] == st_dev["iterations"]
+    assert f_host.isequal(f_dev)
+    f_cc, _ = W.cc_min_label(A)
+    assert f_cc.isequal(f_dev)
+
+
+def test_vector_index_vector_assign_and_extract(gb):
+    """w(min)[I] << u and w << u[I] with I a device vector == the host-index-list forms."""
+    from graphblas_b200 import Vector, binary
+
+    rng = np.random.default_rng(4)
+    n, ni = 500, 2000
+    idx = rng.integers(0, n, size=ni)
+    u = Vector.from_dense(rng.integers(0, 1000, size=ni).astype(np.uint32))
+    w1 = Vector.from_dense(rng.integers(500, 1000, size=n).astype(np.uint32))
+    w2 = w1.dup()
+    Iv = Vector.from_dense(idx.astype(np.uint32))
+    w1(binary.min)[idx] << u
+    w2(binary.min)[Iv] << u
+    assert w1.isequal(w2)
+    src = Vector.from_dense(rng.integers(0, 99, size=n).astype(np.int64))
+    a = src[idx].new()
+    b = Vector("INT64", ni)
+    b << src[Iv]
+    assert a.isequal(b)
+    bad = Vector.from_dense(np.array([n + 5] * ni, dtype=np.uint32))
+    with pytest.raises(gb.IndexOutOfBound):
+        b << src[bad]

@@ -470,6 +470,13 @@ GrB_Info GxB_b200_Matrix_rmat(GrB_Matrix *A, GrB_Type type, int scale, int edgef
                               int symmetrize, int value_mode);
 GrB_Info GxB_b200_rmat_edges_host(uint64_t *src, uint64_t *dst, int scale, uint64_t nedges, uint64_t seed);
 GrB_Info GxB_b200_Matrix_rowblock(GrB_Matrix *C, const GrB_Matrix A, GrB_Index row_begin, GrB_Index row_end);
+/* index lists that already live in HBM: I = the values of a full integer vector (as SuiteSparse 9's GxB_Vector_assign_Vector /
+ * GxB_Vector_extract_Vector).  w<mask>(I) = accum(w(I), u), duplicates folded under MIN/MAX/PLUS; w<mask> = accum(w, u(I)).
+ * FastSV's `f(min)[I] << mngp` and `gp << f[I]` (reference notebooks/Connected Components -- FastSV.ipynb cell 30) with I = f. */
+GrB_Info GxB_b200_Vector_assign_Vector(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Vector u,
+                                       const GrB_Vector I, const GrB_Descriptor desc);
+GrB_Info GxB_b200_Vector_extract_Vector(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum, const GrB_Vector u,
+                                        const GrB_Vector I, const GrB_Descriptor desc);
 /* multi-GPU exchange over NVLink peer memory (csrc/grb_peer.cu; no reference counterpart: python-graphblas is single-process).
  * Vector_wrap_device: a full vector over caller-owned device memory (a symmetric buffer the peers map), so a product's
  *   partial sums land where the other GPUs can read them.
