@@ -519,22 +519,36 @@ static Csr csr_from_host(int64_t nrows, int64_t ncols, const uint64_t *Ap, const
     try { narrow_indices(tmp, nnz, c.colidx, (uint64_t)ncols, "import"); }
     catch (...) { dfree(tmp); csr_free(c); throw; }
     dfree(tmp);
-    if (xcode == out_code) h2d(c.vals, Ax, (size_t)nv * kTypeSize[out_code]);
+    // The values cross PCIe on a second stream, behind the indices, while this stream validates the pattern and -- for a matrix
+    // large enough to be pulled from repeatedly -- builds the stream form of the pull kernels (hub ranking, row flags): on the
+    // PageRank graph 1.7 ms of checking + 1.0 ms of building + the slow first pull used to FOLLOW the 15.4 ms of copies
+    // (tools/debug/e2e_breakdown.py); now they sit under the 4.7 ms the values take.
+    const bool overlap = (xcode == out_code) && nv >= (1 << 20) && g.copy_stream != nullptr;
+    if (overlap) {
+        CUDA_TRY(cudaEventRecord(g.copy_ev_a, g.stream));            // c.vals exists and the index copy is queued
+        CUDA_TRY(cudaStreamWaitEvent(g.copy_stream, g.copy_ev_a, 0));
+        CUDA_TRY(cudaMemcpyAsync(c.vals, Ax, (size_t)nv * kTypeSize[out_code], cudaMemcpyHostToDevice, g.copy_stream));
+        CUDA_TRY(cudaEventRecord(g.copy_ev_b, g.copy_stream));
+    } else if (xcode == out_code) h2d(c.vals, Ax, (size_t)nv * kTypeSize[out_code]);
     else {
         void *sx = dmalloc((size_t)(nv > 0 ? nv : 1) * kTypeSize[xcode]);
         h2d(sx, Ax, (size_t)nv * kTypeSize[xcode]);
         cast_array(sx, xcode, c.vals, out_code, nv);
         dfree(sx);
     }
+    // join: the main stream waits for the values, and so does the host -- the caller may reuse or free Ax when this returns
+    auto join = [&]() { if (overlap) { cudaStreamWaitEvent(g.stream, g.copy_ev_b, 0); cudaEventSynchronize(g.copy_ev_b); } };
     int64_t last = read_i64(c.rowptr + nrows);
     if (last != nnz) {
-        if (last > nnz || last < 0) { csr_free(c); grb_throw(GrB_INVALID_VALUE, "Ap[nrows] exceeds the index array"); }
+        if (last > nnz || last < 0) { join(); stream_sync(); csr_free(c); grb_throw(GrB_INVALID_VALUE, "Ap[nrows] exceeds the index array"); }
         c.nnz = last;
     }
     try {
         bool sorted = csr_is_sorted(c);
-        if (!sorted) { (void)maybe_jumbled; csr_sort_rows(c, out_code); }
-    } catch (...) { csr_free(c); throw; }
+        if (!sorted) { (void)maybe_jumbled; join(); csr_sort_rows(c, out_code); }      // sorting permutes the values: they must have arrived
+        else if (overlap && g.hub_mode && c.nnz >= (1 << 20)) csr_ensure_hubs(c, hub_capacity_for(kTypeSize[out_code]));
+    } catch (...) { join(); stream_sync(); csr_free(c); throw; }
+    join();
     return c;
 }
 

@@ -173,6 +173,9 @@ static GrB_Info do_init(GrB_Mode mode) {
         CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
         CUDA_TRY(cudaMalloc((void **)&g.d_scratch, 64 * sizeof(int64_t)));
         CUDA_TRY(cudaMallocHost((void **)&g.h_pinned, 64 * sizeof(int64_t)));
+        CUDA_TRY(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&g.copy_ev_a, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&g.copy_ev_b, cudaEventDisableTiming));
         const char *b = getenv("GRB_B200_BURBLE");
         g.burble = b ? atoi(b) : 0;
     } catch (const GrbError &err) {

@@ -168,6 +168,8 @@ struct GrbGlobal {
     int device = -1;
     int sm_count = 148;
     cudaStream_t stream = 0;
+    cudaStream_t copy_stream = nullptr;   // second stream: the values of an imported matrix cross PCIe while the indices are checked
+    cudaEvent_t copy_ev_a = nullptr, copy_ev_b = nullptr;
     void *(*h_malloc)(size_t) = malloc;
     void (*h_free)(void *) = free;
     uint64_t launches = 0;
@@ -254,6 +256,7 @@ void mat_ensure_csc(GB_Object *o);                        // build + cache the t
 void csr_transpose(const Csr &a, Csr &t, size_t tsize);
 void csr_ensure_tiles(Csr &c, int tile_nnz);
 void csr_ensure_hubs(Csr &c, int capacity);
+int hub_capacity_for(size_t tsize);                       // hub-table entries k_spmv_red holds for values of tsize bytes (grb_mxv.cu)
 void csr_ensure_tile_blocks(Csr &c, int64_t rows_per_block, int nblocks, int64_t tstep);   // needs the stream form (csr_ensure_hubs)               // build / rebuild the hub cache for at most `capacity` hubs
 void csr_ensure_panels(Csr &c, int npanels, const void *vals, int tcode);   // split by column ranges (values in tcode)
 void csr_drop_caches(Csr &c);                             // tiles + hubs (after the pattern changed)

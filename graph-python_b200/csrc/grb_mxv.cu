@@ -53,6 +53,8 @@ bool spmv_launch_push(int mon, int mul, int tcode, const void *pa) {
     return false;
 }
 
+int hub_capacity_for(size_t tsize) { return tsize > 4 ? hub_capacity<double>() : hub_capacity<float>(); }
+
 template <class T> static T monoid_identity(int mon) {
     switch (mon) {
     case OP_MIN:
