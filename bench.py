@@ -59,7 +59,7 @@ def parse_args():
                          "partition with NCCL reduce-scatter; row = round 1's row blocks + NCCL all-gather of w")
     ap.add_argument("--peer-carveout", type=int, default=-2, help="library option peer_carveout (percent; -1 = driver default)")
     ap.add_argument("--peer-ctas", type=int, default=0, help="CTAs of the peer exchange kernel (0 = 148 fused / 296 peer)")
-    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "fastsv", "spgemm", "tc"],
+    ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "fastsv", "spgemm", "tc", "bfs"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
                          "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
@@ -67,6 +67,7 @@ def parse_args():
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
     ap.add_argument("--no-legs", action="store_true", help="skip the bounded legs of BASELINE configs[0], [2], [3] (bfs / sssp / tc keys)")
     ap.add_argument("--sssp-scale", type=int, default=24)
+    ap.add_argument("--bfs-scale", type=int, default=24, help="N > 1: scale of the sharded level-BFS leg (strong scaling)")
     ap.add_argument("--tc-scale", type=int, default=22)
     return ap.parse_args()
 
@@ -1129,6 +1130,16 @@ def run_b200(args):
             leg = {"error": f"{type(exc).__name__}: {exc}"}
         if rank == 0:
             line["sssp"] = leg
+        # configs[0]'s statement over the N GPUs by push: sources sharded, partial frontiers merged with an all-reduce(max)
+        torch.cuda.empty_cache()
+        try:
+            leg = measure_bfs_sharded(gb, args.bfs_scale, rank, world)
+        except AssertionError:
+            raise
+        except Exception as exc:
+            leg = {"error": f"{type(exc).__name__}: {exc}"}
+        if rank == 0:
+            line["bfs"] = leg
     if rank == 0 and world == 1 and args.extra:
         if args.breakdown:
             gb.lib.GxB_b200_kernel_time_reset()
@@ -1635,6 +1646,211 @@ def measure_sssp(gb, scale, rank, world, steps=3):
     return out if rank == 0 else None
 
 
+# ---------------------------------------------------------------------------------------------- configs[0] over N GPUs: push
+class BfsJob:
+    """Level BFS over N GPUs by PUSH (frontier scatter into a partial buffer + a max-reduction of the partials).
+
+    Rank p owns the SOURCE vertices [lo, hi): its rows of A (`GxB_b200_Matrix_rowblock`, nb x n).  The frontier q and the levels
+    v are replicated (n bytes / 4n bytes; the matrix is what is large).  Per level, as the reference's notebook writes it
+    (notebooks/Example B.1 -- Level BFS.ipynb cell 8) with the product cut by source block:
+        v(q.V)[:] << level
+        t(~v.S, replace=True) << q[lo:hi].vxm(A[lo:hi, :], any_pair)      # this rank's partial: all n targets, from its sources
+        all-reduce(max) of t's presence bytes over the ranks              # any = lor = max on {0, 1}
+        q = t
+    The library picks the direction of the local product as at N = 1: a scatter from the frontier's rows while it is sparse, the
+    masked early-exit pull over the cached transpose of the block when it is not.  Every partial is masked by the replicated
+    ~v.S, so the reduced t is already the next frontier."""
+
+    def __init__(self, gb, scale, rank, world, keep_reference=True):
+        import torch
+        from graphblas_b200 import Matrix, workloads as W
+        from graphblas_b200.sharding import row_block
+
+        self.gb, self.rank, self.world, self.n, self.scale = gb, rank, world, 1 << scale, scale
+        n = self.n
+        A = Matrix.rmat(scale, "BOOL", symmetrize=True)                      # same graph on every rank
+        self.nnz_total = A.nvals
+        rp = gb.ffi.new("void**")
+        gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
+        rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
+        self.deg = (rowptr[1:] - rowptr[:-1]).clone()
+        self.source = int(torch.argmax(self.deg).item())
+        self.lo, self.hi = row_block(n, rank, world)
+        self.reference = None
+        if world == 1:
+            self.A = A
+        else:
+            if keep_reference:                                               # the one-GPU traversal of the same graph, for parity
+                v, st = W.bfs_levels(A, self.source)
+                vv, vp = self._tensors(v, n, "<i4")
+                self.reference = (vv.clone(), vp.clone(), st["frontier_sizes"])
+                del v
+            self.P = A.rowblock(self.lo, self.hi)
+            del A
+        self.nnz_local = (self.A if world == 1 else self.P).nvals
+        self.levels, self.frontier_sizes, self.v = 0, [], None
+        gb.sync()
+
+    def _tensors(self, v, n, typestr="|u1"):
+        gb = self.gb
+        vals, pres = gb.ffi.new("void**"), gb.ffi.new("void**")
+        assert gb.lib.GxB_b200_Vector_device_ptrs(vals, pres, v._carg) == gb.lib.GrB_SUCCESS
+        return (dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), n, typestr),
+                dev_tensor(int(gb.ffi.cast("uintptr_t", pres[0])), n, "|u1"))
+
+    def step(self, trace=None):
+        import torch
+        import torch.distributed as dist
+        from graphblas_b200 import Vector, semiring, workloads as W
+
+        gb, n, lo, hi = self.gb, self.n, self.lo, self.hi
+        if self.world == 1 and trace is None:
+            self.v, st = W.bfs_levels(self.A, self.source)
+            self.levels, self.frontier_sizes = st["levels"], st["frontier_sizes"]
+            return
+        if self.world == 1:
+            self.P = self.A
+        nb = hi - lo
+        v = Vector("INT32", n)
+        q, t, qb = Vector("BOOL", n), Vector("BOOL", n), Vector("BOOL", nb)
+        q[self.source] = True
+        level, sizes = 0, []
+        while True:
+            level += 1
+            nq = q.nvals
+            if nq == 0:
+                break
+            sizes.append(nq)
+            v(q.V)[:] << level
+            qv, qp = self._tensors(q, n)
+            bv, bp = self._tensors(qb, nb)
+            bv.copy_(qv[lo:hi])                                   # q[lo:hi]: the sources this rank pushes from
+            bp.copy_(qp[lo:hi])
+            gb.lib.GxB_b200_Vector_set_dense_nvals(qb._carg, -1)
+            if trace is not None:
+                torch.cuda.synchronize()
+                gb.lib.GxB_b200_kernel_time_reset()
+                gb.set_option("timing", 1)
+                nloc = qb.nvals
+            t(~v.S, replace=True) << qb.vxm(self.P, semiring.any_pair)
+            if trace is not None:
+                torch.cuda.synchronize()
+                gb.set_option("timing", 0)
+                trace.append({"level": level, "frontier": nq, "local_frontier": nloc,
+                              "pull_any_us": kernel_time(gb, "pull_any")[0] * 1e3, "push_scatter_us": kernel_time(gb, "push_scatter")[0] * 1e3,
+                              "writeback_us": kernel_time(gb, "vec_writeback")[0] * 1e3})
+            tv, tp = self._tensors(t, n)
+            if self.world > 1:
+                dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+            tv.fill_(1)
+            gb.lib.GxB_b200_Vector_set_dense_nvals(t._carg, -1)
+            q, t = t, q
+        self.v, self.levels, self.frontier_sizes = v, level - 1, sizes
+
+    def check(self):
+        """Bit-exact parity of the sharded traversal with the one-GPU traversal of the same graph (every rank holds both)."""
+        import torch
+
+        if self.reference is None:
+            return None
+        rv, rp, rsizes = self.reference
+        vv, vp = self._tensors(self.v, self.n, "<i4")
+        m = rp.bool()
+        ok = bool(torch.equal(vp, rp)) and bool(torch.equal(vv[m], rv[m])) and list(rsizes) == list(self.frontier_sizes)
+        return ok
+
+
+def measure_bfs_sharded(gb, scale, rank, world, reps=5, breakdown=False):
+    """Level BFS with the source vertices sharded over `world` GPUs (BfsJob): device time of one traversal (max over ranks), TEPS by
+    the Graph500 convention, and bit-exact parity with the one-GPU traversal of the same graph, asserted.  Rank 0 returns the dict."""
+    import torch
+    import torch.distributed as dist
+
+    job = BfsJob(gb, scale, rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        job.step()                                             # warm-up: cached transpose of the block, NCCL channels
+    ok = job.check()
+    times = []
+    l0 = gb.launch_count()
+    for _ in range(reps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        job.step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        times.append(float(t.item()))
+    launches = (gb.launch_count() - l0) // reps
+    if breakdown:                                              # per-kernel device times of one more traversal (rank 0 prints)
+        gb.lib.GxB_b200_kernel_time_reset()
+        gb.set_option("timing", 1)
+        job.step()
+        barrier()
+        gb.set_option("timing", 0)
+        if rank == 0:
+            gb.lib.GxB_b200_kernel_time_dump()
+        trace = []
+        job.step(trace=trace)
+        barrier()
+        print(f"[bfs trace rank {rank}] " + json.dumps(trace), file=sys.stderr, flush=True)
+    vv, vp = job._tensors(job.v, job.n, "<i4")
+    m = vp.bool()
+    edges = int(job.deg[m].sum().item())
+    ms = float(np.median(times))
+    if world > 1:
+        assert ok, "bench.py: the sharded BFS levels differ from the one-GPU traversal of the same graph"
+    out = {"workload": f"level BFS any_pair masked vxm, symmetrised R-MAT scale {scale}, source vertices (rows of A) sharded over {world} "
+                       f"GPU(s), push/pull chosen per level by the library, one all-reduce(max) of the n presence bytes per level",
+           "value": edges / ms / 1e6, "unit": "GTEPS (edges of the traversed component / time)", "ms": ms, "ms_best": min(times),
+           "n_gpus": world, "scaling": "strong", "levels": job.levels, "frontier_sizes": job.frontier_sizes, "reached": int(m.sum().item()),
+           "edges_traversed": edges, "nnz": job.nnz_total, "gpu_launches": int(launches),
+           "level_checksum": int(vv[m].to(torch.int64).sum().item()),
+           "parity_vs_single_gpu": {"bit_exact": ok, "what": "level vector and frontier sizes of the one-GPU bfs_levels on the same graph"} if world > 1 else None,
+           "collective": {"name": "ncclAllReduce(max, uint8)", "bytes_per_level": job.n, "calls_per_level": 1} if world > 1 else None,
+           "bound": "latency: per level one host read of nvals(q), two block copies, the product and an n-byte all-reduce"}
+    del job
+    return out if rank == 0 else None
+
+
+def run_bfs(args):
+    """`bench.py --workload bfs [--gpus N] [--scale S]`: BASELINE configs[0]'s statement at a FIXED scale over N GPUs (strong scaling);
+    one step = one traversal from the highest-degree vertex."""
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: libgrb_b200 has no CPU fallback"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    import graphblas_b200 as gb
+
+    gb.init("b200")
+    gb.use_torch_stream()
+    with ClockSampler(local_rank) as clk:
+        clk.mark_begin()
+        leg = measure_bfs_sharded(gb, args.scale, rank, world, reps=max(args.steps, 3), breakdown=args.breakdown)
+        clk.mark_end()
+    if rank == 0:
+        line = {"metric": METRIC, "value": leg["value"], "unit": "GTEPS", "n_gpus": world, "steps": max(args.steps, 3), "warmup": 2,
+                "ms_per_step": leg["ms"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bool",
+                "data": "synthetic", "config": {"workload": leg["workload"], "scale": args.scale, "nnz": leg["nnz"]},
+                "gpu_launches": leg["gpu_launches"], "bfs": leg, "roofline": None, "clocks": clk.summary()}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 # ---------------------------------------------------------------------------------------------- configs[3], [4]: sharded mxm
 def run_sharded_mxm(args):
     """`bench.py --workload spgemm|tc [--gpus N] [--scale S]`: GrB_mxm with the rows of A (SpGEMM) or of the mask (triangle
@@ -1815,6 +2031,8 @@ def main():
         run_sssp(args)
     elif args.workload in ("spgemm", "tc"):
         run_sharded_mxm(args)
+    elif args.workload == "bfs":
+        run_bfs(args)
     else:
         run_b200(args)
 

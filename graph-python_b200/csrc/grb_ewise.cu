@@ -88,7 +88,10 @@ __global__ void __launch_bounds__(256) k_assign_scalar(EpiArgs<T> e, T x, int64_
     for (int k = 0; k < EW_VEC; k++) {
         const int64_t i = base + k * 256;
         al[k] = wh[k] = false; wo[k] = (T)0;
-        if (i < n) { al[k] = epi_allowed(e, i); wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+        if (i < n) {
+            al[k] = epi_allowed(e, i);
+            if (epi_reads_old(e, al[k])) { wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+        }
     }
 #pragma unroll
     for (int k = 0; k < EW_VEC; k++) { const int64_t i = base + k * 256; if (i < n) c += epi_apply(e, i, al[k], true, x, wh[k], wo[k]); }
@@ -186,7 +189,8 @@ __global__ void __launch_bounds__(256) k_ewise_fused(const X *u, const uint8_t *
         pa[k] = pb[k] = al[k] = wh[k] = false; xv[k] = yv[k] = (X)0; wo[k] = (Z)0;
         if (i < n) {
             pa[k] = up[i] != 0; pb[k] = vp[i] != 0; xv[k] = u[i]; yv[k] = v[i];
-            al[k] = epi_allowed(e, i); wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i];
+            al[k] = epi_allowed(e, i);
+            if (epi_reads_old(e, al[k])) { wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
         }
     }
 #pragma unroll

@@ -108,18 +108,21 @@ template <class T> __device__ __forceinline__ bool epi_allowed(const EpiArgs<T> 
 // C API 2.0 write-back for one position; returns the final presence (for the nvals counter)
 template <class T>
 __device__ __forceinline__ int epi_store(const EpiArgs<T> &e, int64_t i, bool allowed, bool t_has, T t) {
-    bool w_has = e.wp_in[i] != 0;
-    bool inplace = (e.w_out == e.w_in);
+    // w's old presence is read only on the paths that need it.  Reading it up front made an in-place masked write-back
+    // (`t(~v.S, replace) << q.vxm(A)`, t != q) 2.7x slower than the same product written to a spare buffer: every warp loaded a
+    // line of w's presence bytes that neighbouring warps were storing to (same instructions, same DRAM bytes, three times the
+    // load latency in ncu, profiles/r02_bfs_pull_any_inplace.md).
     if (allowed) {
         if (t_has) {
             T v = t;
-            if (e.accum >= 0 && w_has) v = binop_rt<T>(e.accum, e.w_in[i], t);
+            if (e.accum >= 0 && e.wp_in[i] != 0) v = binop_rt<T>(e.accum, e.w_in[i], t);
             e.w_out[i] = v; e.wp_out[i] = 1;
             return 1;
         }
         if (e.accum < 0) { e.wp_out[i] = 0; return 0; }     // Z = T has no entry here: delete
     } else if (e.replace) { e.wp_out[i] = 0; return 0; }
-    if (!inplace) { e.wp_out[i] = w_has; if (w_has) e.w_out[i] = e.w_in[i]; }
+    const bool w_has = e.wp_in[i] != 0;
+    if (e.w_out != e.w_in) { e.wp_out[i] = w_has; if (w_has) e.w_out[i] = e.w_in[i]; }
     return w_has ? 1 : 0;
 }
 // one global atomic per CTA (every thread of the CTA must call it): same-address atomics from every warp of a
@@ -153,6 +156,9 @@ __device__ __forceinline__ int epi_apply(const EpiArgs<T> &e, int64_t i, bool al
     return w_has ? 1 : 0;
 }
 template <class T> __device__ __forceinline__ bool epi_needs_old(const EpiArgs<T> &e) { return e.accum >= 0 || e.w_out != e.w_in; }
+// does the write-back of one position look at w's old presence / value at all?  An allowed position without accumulator is
+// overwritten or deleted, a masked-out one under `replace` is deleted: neither reads w (see epi_store on why that matters)
+template <class T> __device__ __forceinline__ bool epi_reads_old(const EpiArgs<T> &e, bool allowed) { return allowed ? e.accum >= 0 : !e.replace; }
 constexpr int EW_VEC = 4;            // elements per thread per pass of the element-wise kernels (loads batched)
 static inline int ew_grid4(int64_t n) { int64_t b = (n + 256 * EW_VEC - 1) / (256 * EW_VEC); return (int)(b < 1 ? 1 : b); }
 __device__ __forceinline__ void block_count_add(unsigned long long *count, int c) {
@@ -954,27 +960,50 @@ __global__ void k_gather_hubs(const T *u, const uint8_t *up, const uint32_t *hub
 }
 
 // ---- masked pull with early exit (ANY monoid): one thread per row, stop at the first hit ----
+// A lane scans the first PULL_ANY_SERIAL entries of its row alone (on a BFS level that is worth pulling, most rows hit within
+// two).  Rows still undecided after that are finished by the whole warp, 32 entries per step with one ballot: a single lane
+// walking a 300-entry row costs 300 dependent L2 round trips, and the longest such row set the kernel's time (it is what made
+// the pull over a rank's column block, where a row's frontier neighbours may all live on another rank, 3x slower than the
+// pull over the whole matrix).  The first hit in row order is taken either way, as the oracle does.
+constexpr int PULL_ANY_SERIAL = 8;
 template <class SR>
 __global__ void __launch_bounds__(256) k_pull_any(PullArgs<typename SR::type> a) {
     using T = typename SR::type;
     const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool full = (a.up == nullptr);
+    const bool allowed = r < a.nrows && epi_allowed(a.epi, r);
+    long long p = 0, e = 0, hit = -1;
+    if (allowed) {
+        p = a.rowptr[r]; e = a.rowptr[r + 1];
+        const long long stop = p + PULL_ANY_SERIAL < e ? p + PULL_ANY_SERIAL : e;
+        for (; p < stop; p++)
+            if (full || __ldg(a.up + __ldg(a.col + p))) { hit = p; break; }
+    }
+    unsigned pending = __ballot_sync(0xffffffffu, hit < 0 && p < e);
+    while (pending) {
+        const int src = __ffs(pending) - 1;
+        pending &= pending - 1;
+        const long long ps = __shfl_sync(0xffffffffu, p, src), es = __shfl_sync(0xffffffffu, e, src);
+        long long found = -1;
+        for (long long base = ps; base < es; base += 32) {
+            const long long q = base + lane;
+            const bool h = q < es && (full || __ldg(a.up + __ldg(a.col + q)));
+            const unsigned b = __ballot_sync(0xffffffffu, h);
+            if (b) { found = base + (__ffs(b) - 1); break; }
+        }
+        if (lane == src) hit = found;
+    }
     int my_count = 0;
     if (r < a.nrows) {
-        bool allowed = epi_allowed(a.epi, r);
-        bool has = false; T acc = (T)0;
-        if (allowed) {
-            const bool full = (a.up == nullptr);
-            for (int64_t p = a.rowptr[r], e = a.rowptr[r + 1]; p < e; p++) {
-                uint32_t c = __ldg(a.col + p);
-                if (full || __ldg(a.up + c)) {
-                    T av = SR::kUsesX ? a.av[a.a_iso ? 0 : p] : (T)0;
-                    T x = SR::kUsesY ? a.u[c] : (T)0;
-                    acc = SR::mult(av, x); has = true;
-                    break;
-                }
-            }
+        T acc = (T)0;
+        if (hit >= 0) {
+            const uint32_t c = __ldg(a.col + hit);
+            T av = SR::kUsesX ? a.av[a.a_iso ? 0 : hit] : (T)0;
+            T x = SR::kUsesY ? a.u[c] : (T)0;
+            acc = SR::mult(av, x);
         }
-        my_count = epi_store(a.epi, r, allowed, has, acc);
+        my_count = epi_store(a.epi, r, allowed, hit >= 0, acc);
     }
     block_count_add(a.epi.count, my_count);
 }
@@ -990,7 +1019,10 @@ __global__ void __launch_bounds__(256) k_vec_writeback(EpiArgs<T> e, const T *t,
     for (int k = 0; k < EW_VEC; k++) {
         const int64_t i = base + k * 256;
         al[k] = th[k] = wh[k] = false; tv[k] = wo[k] = (T)0;
-        if (i < n) { al[k] = epi_allowed(e, i); th[k] = tp[i] != 0; tv[k] = t[i]; wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+        if (i < n) {
+            al[k] = epi_allowed(e, i); th[k] = tp[i] != 0; tv[k] = t[i];
+            if (epi_reads_old(e, al[k])) { wh[k] = e.wp_in[i] != 0; if (need_old) wo[k] = e.w_in[i]; }
+        }
     }
 #pragma unroll
     for (int k = 0; k < EW_VEC; k++) {

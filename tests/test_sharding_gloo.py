@@ -195,3 +195,60 @@ def test_sharded_triangle_count_matches_single_process(tmp_path):
     dense[r, c] = 1
     assert int(got[0]) == int(np.trace(dense @ dense @ dense) // 6)
     assert int(got[1]) == A.nnz // 2
+
+
+# ---- level BFS by push over the source blocks (bench.py BfsJob): partial frontiers merged with an all-reduce(max) ----
+def _bfs_worker(rank, world, port, scale, src, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = O.rmat_matrix(scale, "BOOL", symmetrize=True)
+        n = A.shape[0]
+        lo, hi = row_block(n, rank, world)
+        Pb = _block(A, lo, hi)                                   # my source vertices: rows [lo, hi) of A
+        lv = O.Vec.empty(n, "INT32")
+        q = O.Vec.from_coo([src], [True], n, "BOOL")
+        level, sizes = 0, []
+        while q.nvals:
+            level += 1
+            sizes.append(int(q.nvals))
+            m = q.present.astype(bool)
+            lv.values[m] = level
+            lv.present[m] = 1
+            qb = O.Vec(q.values[lo:hi].copy(), q.present[lo:hi].copy(), "BOOL")
+            t = O.Vec.empty(n, "BOOL")
+            O.vxm(t, qb, Pb, "ANY", "PAIR", "BOOL", mask=lv, comp=True, structure=True, replace=True)
+            tp = torch.from_numpy(t.present.astype(np.uint8))
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+            q = O.Vec(np.ones(n, dtype=np.bool_), tp.numpy().copy(), "BOOL")
+        if rank == 0:
+            np.savez(out, values=lv.values, present=lv.present, sizes=np.array(sizes))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_push_bfs_matches_single_process(tmp_path, world):
+    scale = 9
+    A = O.rmat_matrix(scale, "BOOL", symmetrize=True)
+    n = A.shape[0]
+    src = int(np.argmax(np.diff(A.indptr)))
+    out = str(tmp_path / "bfs.npz")
+    mp.spawn(_bfs_worker, args=(world, _free_port(), scale, src, out), nprocs=world, join=True)
+    got = np.load(out)
+    lv = O.Vec.empty(n, "INT32")
+    q = O.Vec.from_coo([src], [True], n, "BOOL")
+    level, sizes = 0, []
+    while q.nvals:
+        level += 1
+        sizes.append(int(q.nvals))
+        m = q.present.astype(bool)
+        lv.values[m] = level
+        lv.present[m] = 1
+        nq = O.Vec.empty(n, "BOOL")
+        O.vxm(nq, q, A, "ANY", "PAIR", "BOOL", mask=lv, comp=True, structure=True, replace=True, At=A)
+        q = nq
+    p = lv.present.astype(bool)
+    assert np.array_equal(got["present"].astype(bool), p)
+    assert np.array_equal(got["values"][p], lv.values[p])
+    assert list(got["sizes"]) == sizes and len(sizes) >= 3
