@@ -1648,34 +1648,38 @@ def measure_sssp(gb, scale, rank, world, steps=3):
 
 # ---------------------------------------------------------------------------------------------- configs[0] over N GPUs: push
 class BfsJob:
-    """Level BFS over N GPUs by PUSH (frontier scatter into a partial buffer + a max-reduction of the partials).
+    """Direction-optimising level BFS over N GPUs, vertices in 1-D blocks.
 
-    Rank p owns the SOURCE vertices [lo, hi): its rows of A (`GxB_b200_Matrix_rowblock`, nb x n).  The frontier q and the levels
-    v are replicated (n bytes / 4n bytes; the matrix is what is large).  Per level, as the reference's notebook writes it
-    (notebooks/Example B.1 -- Level BFS.ipynb cell 8) with the product cut by source block:
-        v(q.V)[:] << level
-        t(~v.S, replace=True) << q[lo:hi].vxm(A[lo:hi, :], any_pair)      # this rank's partial: all n targets, from its sources
-        all-reduce(max) of t's presence bytes over the ranks              # any = lor = max on {0, 1}
-        q = t
-    The library picks the direction of the local product as at N = 1: a scatter from the frontier's rows while it is sparse, the
-    masked early-exit pull over the cached transpose of the block when it is not.  Every partial is masked by the replicated
-    ~v.S, so the reduced t is already the next frontier."""
+    Rank p owns the vertices [lo, hi): their levels vb, their part qb of the frontier, and two row blocks of the matrix:
+    A[lo:hi, :] (its SOURCES, for the push) and A'[lo:hi, :] (its TARGETS, for the pull).  Per level, the statement of the
+    reference's notebook (notebooks/Example B.1 -- Level BFS.ipynb cell 8: `q(~v.S, replace=True) << q.vxm(A, any_pair)`) is
+    evaluated in the direction the library's own rule picks for the GLOBAL frontier (sharding.push_is_cheaper):
+      push:  t << qb.vxm(A[lo:hi, :])                     frontier scatter from this rank's sources into a partial over all n
+             reduce-scatter(max) of the presence bytes    any = lor = max on {0, 1}; this rank receives its own targets
+             qb(~vb.S, replace=True) << (its block)
+      pull:  all-gather of the frontier blocks            n presence bytes in total
+             qb(~vb.S, replace=True) << A'[lo:hi, :].mxv(q, any_pair)       masked early-exit pull over this rank's targets only
+    The frontier size and the edges leaving it are summed over the ranks with one two-word all-reduce per level, which is also
+    the loop test (the notebook reads q.nvals there)."""
 
     def __init__(self, gb, scale, rank, world, keep_reference=True):
         import torch
-        from graphblas_b200 import Matrix, workloads as W
-        from graphblas_b200.sharding import row_block
+        from graphblas_b200 import Matrix, Vector, workloads as W
+        from graphblas_b200.sharding import BlockExchange
 
         self.gb, self.rank, self.world, self.n, self.scale = gb, rank, world, 1 << scale, scale
+        self._views, self._pp = {}, (gb.ffi.new("void**"), gb.ffi.new("void**"))
         n = self.n
         A = Matrix.rmat(scale, "BOOL", symmetrize=True)                      # same graph on every rank
         self.nnz_total = A.nvals
         rp = gb.ffi.new("void**")
         gb.lib.GxB_b200_Matrix_device_ptrs(rp, gb.ffi.NULL, gb.ffi.NULL, A._carg)
         rowptr = dev_tensor(int(gb.ffi.cast("uintptr_t", rp[0])), n + 1, "<i8")
-        self.deg = (rowptr[1:] - rowptr[:-1]).clone()
-        self.source = int(torch.argmax(self.deg).item())
-        self.lo, self.hi = row_block(n, rank, world)
+        deg = rowptr[1:] - rowptr[:-1]
+        self.source = int(torch.argmax(deg).item())
+        self.ex = BlockExchange(n, rank, world)
+        self.lo, self.hi = self.ex.lo, self.ex.hi
+        self.deg_b = deg[self.lo:self.hi].clone()                            # out-degrees of my vertices
         self.reference = None
         if world == 1:
             self.A = A
@@ -1683,81 +1687,119 @@ class BfsJob:
             if keep_reference:                                               # the one-GPU traversal of the same graph, for parity
                 v, st = W.bfs_levels(A, self.source)
                 vv, vp = self._tensors(v, n, "<i4")
-                self.reference = (vv.clone(), vp.clone(), st["frontier_sizes"])
+                self.reference = (vv[self.lo:self.hi].clone(), vp[self.lo:self.hi].clone(), st["frontier_sizes"])
                 del v
-            self.P = A.rowblock(self.lo, self.hi)
+            self.P_push = A.rowblock(self.lo, self.hi)                       # my sources
+            AT = A.T.new()
             del A
-        self.nnz_local = (self.A if world == 1 else self.P).nvals
-        self.levels, self.frontier_sizes, self.v = 0, [], None
+            self.P_pull = AT.rowblock(self.lo, self.hi)                      # my targets
+            del AT
+            self.stat = torch.zeros(2, dtype=torch.int64, device="cuda")
+        self.nnz_local = (self.A if world == 1 else self.P_push).nvals
+        self.levels, self.frontier_sizes, self.directions, self.vb = 0, [], [], None
         gb.sync()
 
     def _tensors(self, v, n, typestr="|u1"):
+        """torch views of a vector's value and presence buffers.  The library ping-pongs between two buffers per vector and its
+        pool hands the same addresses back traversal after traversal, so the views are cached by address: building one from
+        __cuda_array_interface__ costs tens of microseconds of host time, several times per level."""
         gb = self.gb
-        vals, pres = gb.ffi.new("void**"), gb.ffi.new("void**")
+        vals, pres = self._pp
         assert gb.lib.GxB_b200_Vector_device_ptrs(vals, pres, v._carg) == gb.lib.GrB_SUCCESS
-        return (dev_tensor(int(gb.ffi.cast("uintptr_t", vals[0])), n, typestr),
-                dev_tensor(int(gb.ffi.cast("uintptr_t", pres[0])), n, "|u1"))
+        out = []
+        for ptr, ts in ((int(gb.ffi.cast("uintptr_t", vals[0])), typestr), (int(gb.ffi.cast("uintptr_t", pres[0])), "|u1")):
+            key = (ptr, n, ts)
+            t = self._views.get(key)
+            if t is None:
+                if len(self._views) > 256:
+                    self._views.clear()
+                t = self._views[key] = dev_tensor(ptr, n, ts)
+            out.append(t)
+        return out
 
-    def step(self, trace=None):
+    def step(self):
         import torch
         import torch.distributed as dist
         from graphblas_b200 import Vector, semiring, workloads as W
+        from graphblas_b200.sharding import push_is_cheaper
 
         gb, n, lo, hi = self.gb, self.n, self.lo, self.hi
-        if self.world == 1 and trace is None:
-            self.v, st = W.bfs_levels(self.A, self.source)
-            self.levels, self.frontier_sizes = st["levels"], st["frontier_sizes"]
-            return
         if self.world == 1:
-            self.P = self.A
+            self.vb, st = W.bfs_levels(self.A, self.source)
+            self.levels, self.frontier_sizes, self.directions = st["levels"], st["frontier_sizes"], None
+            return
         nb = hi - lo
-        v = Vector("INT32", n)
-        q, t, qb = Vector("BOOL", n), Vector("BOOL", n), Vector("BOOL", nb)
-        q[self.source] = True
-        level, sizes = 0, []
+        vb = Vector("INT32", nb)
+        qb, cb = Vector("BOOL", nb), Vector("BOOL", nb)
+        q, t = Vector("BOOL", n), Vector("BOOL", n)
+        if lo <= self.source < hi:
+            qb[self.source - lo] = True
+        level, sizes, dirs = 0, [], []
         while True:
             level += 1
-            nq = q.nvals
+            bv, bp = self._tensors(qb, nb)
+            self.stat[0] = bp.sum(dtype=torch.int64)
+            self.stat[1] = (self.deg_b * bp).sum()
+            dist.all_reduce(self.stat)
+            nq, edges = (int(x) for x in self.stat.tolist())           # the level's one host read
             if nq == 0:
                 break
             sizes.append(nq)
-            v(q.V)[:] << level
-            qv, qp = self._tensors(q, n)
-            bv, bp = self._tensors(qb, nb)
-            bv.copy_(qv[lo:hi])                                   # q[lo:hi]: the sources this rank pushes from
-            bp.copy_(qp[lo:hi])
-            gb.lib.GxB_b200_Vector_set_dense_nvals(qb._carg, -1)
-            if trace is not None:
-                torch.cuda.synchronize()
-                gb.lib.GxB_b200_kernel_time_reset()
-                gb.set_option("timing", 1)
-                nloc = qb.nvals
-            t(~v.S, replace=True) << qb.vxm(self.P, semiring.any_pair)
-            if trace is not None:
-                torch.cuda.synchronize()
-                gb.set_option("timing", 0)
-                trace.append({"level": level, "frontier": nq, "local_frontier": nloc,
-                              "pull_any_us": kernel_time(gb, "pull_any")[0] * 1e3, "push_scatter_us": kernel_time(gb, "push_scatter")[0] * 1e3,
-                              "writeback_us": kernel_time(gb, "vec_writeback")[0] * 1e3})
-            tv, tp = self._tensors(t, n)
-            if self.world > 1:
-                dist.all_reduce(tp, op=dist.ReduceOp.MAX)
-            tv.fill_(1)
-            gb.lib.GxB_b200_Vector_set_dense_nvals(t._carg, -1)
-            q, t = t, q
-        self.v, self.levels, self.frontier_sizes = v, level - 1, sizes
+            vb(qb.V)[:] << level
+            if push_is_cheaper(nq, edges, n, self.nnz_total):
+                dirs.append("push")
+                gb.set_option("force_direction", 2)
+                t << qb.vxm(self.P_push, semiring.any_pair)
+                gb.set_option("force_direction", 0)
+                tv, tp = self._tensors(t, n)
+                cv, cp = self._tensors(cb, nb)
+                self.ex.reduce_scatter(cp, tp)
+                cv.fill_(1)
+                gb.lib.GxB_b200_Vector_set_dense_nvals(cb._carg, -1)
+                qb(~vb.S, replace=True) << cb
+            else:
+                dirs.append("pull")
+                qv, qp = self._tensors(q, n)
+                bv, bp = self._tensors(qb, nb)
+                self.ex.all_gather(qp, bp)
+                qv.fill_(1)
+                gb.lib.GxB_b200_Vector_set_dense_nvals(q._carg, nq)
+                gb.set_option("force_direction", 1)
+                qb(~vb.S, replace=True) << self.P_pull.mxv(q, semiring.any_pair)
+                gb.set_option("force_direction", 0)
+        self.vb, self.levels, self.frontier_sizes, self.directions = vb, level - 1, sizes, dirs
 
     def check(self):
-        """Bit-exact parity of the sharded traversal with the one-GPU traversal of the same graph (every rank holds both)."""
+        """Bit-exact parity of this rank's block of the levels with the one-GPU traversal of the same graph; all ranks agree."""
         import torch
+        import torch.distributed as dist
 
         if self.reference is None:
             return None
         rv, rp, rsizes = self.reference
-        vv, vp = self._tensors(self.v, self.n, "<i4")
+        vv, vp = self._tensors(self.vb, self.hi - self.lo, "<i4")
         m = rp.bool()
         ok = bool(torch.equal(vp, rp)) and bool(torch.equal(vv[m], rv[m])) and list(rsizes) == list(self.frontier_sizes)
-        return ok
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return bool(flag.item())
+
+    def totals(self):
+        """(vertices reached, edges of the traversed component, sum of the levels) over all ranks."""
+        import torch
+        import torch.distributed as dist
+
+        if self.world == 1:
+            vv, vp = self._tensors(self.vb, self.n, "<i4")
+            deg = self.deg_b
+        else:
+            vv, vp = self._tensors(self.vb, self.hi - self.lo, "<i4")
+            deg = self.deg_b
+        m = vp.bool()
+        part = torch.stack([m.sum(dtype=torch.int64), deg[m].sum(), vv[m].to(torch.int64).sum()])
+        if self.world > 1:
+            dist.all_reduce(part)
+        return tuple(int(x) for x in part.tolist())
 
 
 def measure_bfs_sharded(gb, scale, rank, world, reps=5, breakdown=False):
@@ -1798,25 +1840,21 @@ def measure_bfs_sharded(gb, scale, rank, world, reps=5, breakdown=False):
         gb.set_option("timing", 0)
         if rank == 0:
             gb.lib.GxB_b200_kernel_time_dump()
-        trace = []
-        job.step(trace=trace)
-        barrier()
-        print(f"[bfs trace rank {rank}] " + json.dumps(trace), file=sys.stderr, flush=True)
-    vv, vp = job._tensors(job.v, job.n, "<i4")
-    m = vp.bool()
-    edges = int(job.deg[m].sum().item())
+    reached, edges, checksum = job.totals()
     ms = float(np.median(times))
     if world > 1:
         assert ok, "bench.py: the sharded BFS levels differ from the one-GPU traversal of the same graph"
-    out = {"workload": f"level BFS any_pair masked vxm, symmetrised R-MAT scale {scale}, source vertices (rows of A) sharded over {world} "
-                       f"GPU(s), push/pull chosen per level by the library, one all-reduce(max) of the n presence bytes per level",
+    out = {"workload": f"level BFS any_pair masked vxm/mxv, symmetrised R-MAT scale {scale}, vertices in 1-D blocks over {world} GPU(s); "
+                       "per level the library's direction rule on the global frontier: push = scatter from this rank's sources + "
+                       "reduce-scatter(max) of the presence bytes, pull = all-gather of the frontier + masked early-exit pull over this "
+                       "rank's targets",
            "value": edges / ms / 1e6, "unit": "GTEPS (edges of the traversed component / time)", "ms": ms, "ms_best": min(times),
-           "n_gpus": world, "scaling": "strong", "levels": job.levels, "frontier_sizes": job.frontier_sizes, "reached": int(m.sum().item()),
-           "edges_traversed": edges, "nnz": job.nnz_total, "gpu_launches": int(launches),
-           "level_checksum": int(vv[m].to(torch.int64).sum().item()),
+           "n_gpus": world, "scaling": "strong", "levels": job.levels, "frontier_sizes": job.frontier_sizes, "directions": job.directions,
+           "reached": reached, "edges_traversed": edges, "nnz": job.nnz_total, "gpu_launches": int(launches), "level_checksum": checksum,
            "parity_vs_single_gpu": {"bit_exact": ok, "what": "level vector and frontier sizes of the one-GPU bfs_levels on the same graph"} if world > 1 else None,
-           "collective": {"name": "ncclAllReduce(max, uint8)", "bytes_per_level": job.n, "calls_per_level": 1} if world > 1 else None,
-           "bound": "latency: per level one host read of nvals(q), two block copies, the product and an n-byte all-reduce"}
+           "collective": {"push_level": "ncclReduceScatter(max, uint8), n bytes in, n/N out", "pull_level": "ncclAllGather(uint8), n bytes out",
+                          "per_level": "ncclAllReduce(sum) of two int64 (frontier size, edges leaving it)"} if world > 1 else None,
+           "bound": "latency: per level one host read, a handful of launches and one or two small collectives"}
     del job
     return out if rank == 0 else None
 

@@ -50,7 +50,7 @@ void vec_writeback_any(GB_Object *w, GB_Object *mask, const DescFlags &f, int ac
     dzero(w->d_nvals, sizeof(int64_t));
     GRB_TYPE_SWITCH(wcode, W, {
         EpiArgs<W> e = epi_for<W>(w, mask, f, accum);
-        GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, ew_grid4(n), 256, 0, e, (const W *)t, tp, n);
+        launch_vec_writeback<W>(e, (const W *)t, tp, n);
     });
     dfree(tc);
     vec_set_unknown_nvals(w);
@@ -134,7 +134,11 @@ static GrB_Info vector_assign_scalar(GrB_Vector w_, const GrB_Vector mask_, cons
             w->nvals = n; w->nvals_known = true; w->list_valid = false;
         } else if (all) {
             dzero(w->d_nvals, sizeof(int64_t));
-            GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, ew_grid4(n), 256, 0, e, xv, n);
+            if (writeback16_ok(e, nullptr, nullptr, n)) {
+                auto wide = k_writeback16<W, true>;
+                GRB_LAUNCH("assign_scalar16", wide, writeback16_grid(n), 256, 0, e, (const W *)nullptr, (const uint8_t *)nullptr, xv, n);
+            } else
+                GRB_LAUNCH("assign_scalar", k_assign_scalar<W>, ew_grid4(n), 256, 0, e, xv, n);
             vec_set_unknown_nvals(w);
         } else {
             if (f.replace) grb_throw(GrB_NOT_IMPLEMENTED, "assign with an index list and replace");

@@ -144,7 +144,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
         dzero(w->d_nvals, sizeof(int64_t));
         if (fused) {
             EpiArgs<T> e = make_epi<T>(w, false, mask, f, accum);
-            GRB_LAUNCH("vec_writeback", k_vec_writeback<T>, ew_grid4(n_out), 256, 0, e, tv, tpres, n_out);
+            launch_vec_writeback<T>(e, tv, tpres, n_out);
         } else {
             int wcode = w->type->code;
             void *tc = dmalloc((size_t)(n_out > 0 ? n_out : 1) * w->type->size);
@@ -156,7 +156,7 @@ static void product_typed(GB_Object *w, GB_Object *mask, int accum, int mon, int
             } else cast_array(tv, tcode, tc, wcode, n_out);
             GRB_TYPE_SWITCH(wcode, W, {
                 EpiArgs<W> e = make_epi<W>(w, false, mask, f, accum);
-                GRB_LAUNCH("vec_writeback", k_vec_writeback<W>, ew_grid4(n_out), 256, 0, e, (const W *)tc, tpres, n_out);
+                launch_vec_writeback<W>(e, (const W *)tc, tpres, n_out);
             });
             dfree(tc);
         }

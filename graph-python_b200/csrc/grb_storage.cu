@@ -578,9 +578,8 @@ void vec_build_list(GB_Object *o) {
         CUDA_TRY(cub::DeviceSelect::Flagged(tmp, tb, ids, o->present, o->list, d_num, (int)n, g.stream));
         if (slot >= 0) ktime_end(slot);
         g.launches += 1;
-        const int64_t nv = read_i64(d_num);
+        if (!o->nvals_known) { o->nvals = read_i64(d_num); o->nvals_known = true; }     // known count: no host round trip
         dfree(tmp); dfree(d_num);
-        o->nvals = nv; o->nvals_known = true;
         o->list_valid = true;
         return;
     }

@@ -73,3 +73,30 @@ class BlockExchange:
         dist.all_gather_into_tensor(self._pad, self._mine, group=self.group)
         full.copy_(self._pad[: self.n])
         return full
+
+    def reduce_scatter(self, block, full, op=None):
+        """block = this rank's [lo, hi) slice of the element-wise reduction of every rank's `full` (default: max).
+
+        The push direction of a vector product: every rank scatters from the sources it owns into a full-length partial
+        result, and each rank needs the reduction of its own targets only.  NCCL with equal blocks runs a
+        true reduce-scatter straight between the library's buffers; otherwise (ragged blocks, or gloo on CPU, which has no
+        reduce-scatter) an all-reduce of a copy followed by the slice gives the same result."""
+        op = dist.ReduceOp.MAX if op is None else op
+        assert full.numel() == self.n and block.numel() == self.hi - self.lo
+        if self.world == 1:
+            block.copy_(full)
+            return block
+        if self.even and dist.get_backend(self.group) == "nccl":
+            dist.reduce_scatter_tensor(block, full, op=op, group=self.group)
+            return block
+        tmp = full.clone()
+        dist.all_reduce(tmp, op=op, group=self.group)
+        block.copy_(tmp[self.lo:self.hi])
+        return block
+
+
+def push_is_cheaper(frontier_nvals, frontier_edges, n, nnz, push_ratio=24, push_edge_ratio=4):
+    """The library's direction rule for one vector product (csrc/grb_mxv.cu product_typed), applied to the GLOBAL frontier of a
+    sharded traversal so that every rank takes the same direction: push while the frontier is a small share of the vertices AND
+    the edges leaving it are a small share of the matrix (a few hub vertices own most of an R-MAT graph)."""
+    return frontier_nvals * push_ratio < n and frontier_edges * push_edge_ratio <= nnz

@@ -197,32 +197,57 @@ def test_sharded_triangle_count_matches_single_process(tmp_path):
     assert int(got[1]) == A.nnz // 2
 
 
-# ---- level BFS by push over the source blocks (bench.py BfsJob): partial frontiers merged with an all-reduce(max) ----
+# ---- direction-optimising level BFS over vertex blocks (bench.py BfsJob): push = scatter from my sources + reduce-scatter(max),
+# ---- pull = all-gather of the frontier + masked pull over my targets; the direction follows the global frontier on every rank
+from graphblas_b200.sharding import push_is_cheaper
+
+
 def _bfs_worker(rank, world, port, scale, src, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         A = O.rmat_matrix(scale, "BOOL", symmetrize=True)
         n = A.shape[0]
-        lo, hi = row_block(n, rank, world)
-        Pb = _block(A, lo, hi)                                   # my source vertices: rows [lo, hi) of A
-        lv = O.Vec.empty(n, "INT32")
-        q = O.Vec.from_coo([src], [True], n, "BOOL")
-        level, sizes = 0, []
-        while q.nvals:
+        nnz = int(A.indptr[-1])
+        ex = BlockExchange(n)
+        lo, hi = ex.lo, ex.hi
+        nb = hi - lo
+        P_push = _block(A, lo, hi)                               # my sources: rows [lo, hi) of A
+        P_pull = _block(A.transpose(), lo, hi)                   # my targets: rows [lo, hi) of A'
+        deg_b = np.diff(A.indptr)[lo:hi]
+        vb = O.Vec.empty(nb, "INT32")
+        qb = O.Vec.from_coo([src - lo] if lo <= src < hi else [], [True] if lo <= src < hi else [], nb, "BOOL")
+        level, sizes, dirs = 0, [], []
+        while True:
             level += 1
-            sizes.append(int(q.nvals))
-            m = q.present.astype(bool)
-            lv.values[m] = level
-            lv.present[m] = 1
-            qb = O.Vec(q.values[lo:hi].copy(), q.present[lo:hi].copy(), "BOOL")
-            t = O.Vec.empty(n, "BOOL")
-            O.vxm(t, qb, Pb, "ANY", "PAIR", "BOOL", mask=lv, comp=True, structure=True, replace=True)
-            tp = torch.from_numpy(t.present.astype(np.uint8))
-            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
-            q = O.Vec(np.ones(n, dtype=np.bool_), tp.numpy().copy(), "BOOL")
+            stat = torch.tensor([int(qb.present.sum()), int(deg_b[qb.present.astype(bool)].sum())], dtype=torch.int64)
+            dist.all_reduce(stat)
+            nq, edges = (int(x) for x in stat.tolist())
+            if nq == 0:
+                break
+            sizes.append(nq)
+            m = qb.present.astype(bool)
+            vb.values[m] = level
+            vb.present[m] = 1
+            if push_is_cheaper(nq, edges, n, nnz):
+                dirs.append("push")
+                t = O.Vec.empty(n, "BOOL")
+                O.vxm(t, qb, P_push, "ANY", "PAIR", "BOOL")
+                cp = torch.zeros(nb, dtype=torch.uint8)
+                ex.reduce_scatter(cp, torch.from_numpy(t.present.astype(np.uint8)))
+                cb = O.Vec(np.ones(nb, dtype=np.bool_), cp.numpy().copy(), "BOOL")
+                O.vec_writeback(qb, cb, mask=vb, replace=True, comp=True, structure=True)
+            else:
+                dirs.append("pull")
+                qp = torch.zeros(n, dtype=torch.uint8)
+                ex.all_gather(qp, torch.from_numpy(qb.present.astype(np.uint8)))
+                q = O.Vec(np.ones(n, dtype=np.bool_), qp.numpy().copy(), "BOOL")
+                O.mxv(qb, P_pull, q, "ANY", "PAIR", "BOOL", mask=vb, comp=True, structure=True, replace=True)
+        vals, pres = torch.zeros(n, dtype=torch.int32), torch.zeros(n, dtype=torch.uint8)
+        ex.all_gather(vals, torch.from_numpy(vb.values.astype(np.int32)))
+        ex.all_gather(pres, torch.from_numpy(vb.present.astype(np.uint8)))
         if rank == 0:
-            np.savez(out, values=lv.values, present=lv.present, sizes=np.array(sizes))
+            np.savez(out, values=vals.numpy(), present=pres.numpy(), sizes=np.array(sizes), dirs=np.array(dirs))
     finally:
         dist.destroy_process_group()
 
@@ -252,3 +277,11 @@ def test_sharded_push_bfs_matches_single_process(tmp_path, world):
     assert np.array_equal(got["present"].astype(bool), p)
     assert np.array_equal(got["values"][p], lv.values[p])
     assert list(got["sizes"]) == sizes and len(sizes) >= 3
+    assert {"push", "pull"} <= set(got["dirs"].tolist())        # both directions were taken
+
+
+def test_reduce_scatter_helper_single_process():
+    ex = BlockExchange(10, rank=0, world=1)
+    full, block = torch.arange(10, dtype=torch.uint8), torch.zeros(10, dtype=torch.uint8)
+    assert torch.equal(ex.reduce_scatter(block, full), full)
+    assert push_is_cheaper(1, 10, 1000, 1000) and not push_is_cheaper(100, 10, 1000, 1000) and not push_is_cheaper(1, 900, 1000, 1000)
