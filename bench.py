@@ -1680,6 +1680,7 @@ class BfsJob:
         self.ex = BlockExchange(n, rank, world)
         self.lo, self.hi = self.ex.lo, self.ex.hi
         self.deg_b = deg[self.lo:self.hi].clone()                            # out-degrees of my vertices
+        self.deg_b32 = self.deg_b.to(torch.int32)                            # (the per-level edge count streams these: 4 bytes each)
         self.reference = None
         if world == 1:
             self.A = A
@@ -1734,12 +1735,14 @@ class BfsJob:
         q, t = Vector("BOOL", n), Vector("BOOL", n)
         if lo <= self.source < hi:
             qb[self.source - lo] = True
+        self._tensors(cb, nb)[0].fill_(1)          # cb and q only ever receive presence bytes from a collective: their values are
+        self._tensors(q, n)[0].fill_(1)            # `true` wherever an entry can appear, written once per traversal
         level, sizes, dirs = 0, [], []
         while True:
             level += 1
             bv, bp = self._tensors(qb, nb)
             self.stat[0] = bp.sum(dtype=torch.int64)
-            self.stat[1] = (self.deg_b * bp).sum()
+            self.stat[1] = (self.deg_b32 * bp).sum(dtype=torch.int64)
             dist.all_reduce(self.stat)
             nq, edges = (int(x) for x in self.stat.tolist())           # the level's one host read
             if nq == 0:
@@ -1754,7 +1757,6 @@ class BfsJob:
                 tv, tp = self._tensors(t, n)
                 cv, cp = self._tensors(cb, nb)
                 self.ex.reduce_scatter(cp, tp)
-                cv.fill_(1)
                 gb.lib.GxB_b200_Vector_set_dense_nvals(cb._carg, -1)
                 qb(~vb.S, replace=True) << cb
             else:
@@ -1762,7 +1764,6 @@ class BfsJob:
                 qv, qp = self._tensors(q, n)
                 bv, bp = self._tensors(qb, nb)
                 self.ex.all_gather(qp, bp)
-                qv.fill_(1)
                 gb.lib.GxB_b200_Vector_set_dense_nvals(q._carg, nq)
                 gb.set_option("force_direction", 1)
                 qb(~vb.S, replace=True) << self.P_pull.mxv(q, semiring.any_pair)
