@@ -338,6 +338,10 @@ class PageRankJob:
         n = 1 << scale
         self.n = n
         self.partition = partition if world > 1 else "none"
+        if self.partition in ("row", "col"):
+            # these A/B partitions hand the library's buffers to NCCL through cached torch views between two statements; the
+            # library's deferred element-wise pair (non-blocking mode) only materialises at its own entry points
+            gb.set_option("lazy", 0)
         A = Matrix.rmat(scale, "FP32", value_mode=2)            # rows = sources; same graph on every rank
         self.nnz_total = A.nvals
         rp = gb.ffi.new("void**")

@@ -202,6 +202,7 @@ GrB_Info GxB_init(GrB_Mode mode, void *(*user_malloc)(size_t), void *(*user_call
 
 GrB_Info GrB_finalize(void) {
     if (g.initialized) {
+        if (g.pending_n) { try { pending_flush(); } catch (const GrbError &) {} }
         cudaStreamSynchronize(g.stream);
         g.initialized = false;
     }
@@ -320,12 +321,14 @@ GrB_Info GrB_Type_error(const char **error, const GrB_Type t) { (void)t; if (err
 
 // ---------------- B200 plumbing ----------------
 GrB_Info GxB_b200_set_stream(void *cuda_stream) {
+    if (g.initialized && g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return e.info; } }
     if (g.initialized) cudaStreamSynchronize(g.stream);
     g.stream = (cudaStream_t)cuda_stream;
     return GrB_SUCCESS;
 }
 GrB_Info GxB_b200_sync(void) {
     if (!g.initialized) return GrB_PANIC;
+    if (g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return e.info; } }
     return cudaStreamSynchronize(g.stream) == cudaSuccess ? GrB_SUCCESS : GrB_PANIC;
 }
 GrB_Info GxB_b200_device_info(int *device, int *sm_count, size_t *free_bytes, size_t *total_bytes) {
@@ -374,6 +377,10 @@ GrB_Info GxB_b200_set_option(const char *name, int64_t value) {
     else if (!strcmp(name, "smem_kb")) { if (value < 64 || value > 226) return GrB_INVALID_VALUE; g.smem_kb = value; }
     else if (!strcmp(name, "timing")) { if (!value) ktime_fold(); g.timing = value; }
     else if (!strcmp(name, "peer_carveout")) g.peer_carveout = value;
+    else if (!strcmp(name, "lazy")) {       // 0: never defer element-wise work (grb_internal.cuh PendingOp)
+        if (g.initialized && g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return e.info; } }
+        g.lazy = value;
+    }
     else return GrB_INVALID_VALUE;
     return GrB_SUCCESS;
 }

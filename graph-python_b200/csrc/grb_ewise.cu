@@ -110,8 +110,11 @@ __global__ void k_assign_scalar_list(EpiArgs<T> e, T x, const uint64_t *I, int64
 template <class T>
 static GrB_Info vector_assign_scalar(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, T x, int xcode,
                                      const GrB_Index *I, GrB_Index ni, const GrB_Descriptor desc) {
-    API_BEGIN
+    API_BEGIN_NOFLUSH
     require_init();
+    // a plain fill right behind a deferred element-wise product joins it; anything else runs the queue first
+    const bool may_join = g.pending_n == 1 && g.pending[0].kind == 1 && lazy_on() && !mask_ && !accum && I == GrB_ALL;
+    if (g.pending_n && !may_join) pending_flush();
     GB_Object *w = obj_check(w_, "w");
     GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
     check_vec(w, "w");
@@ -119,6 +122,19 @@ static GrB_Info vector_assign_scalar(GrB_Vector w_, const GrB_Vector mask_, cons
     DescFlags f = desc_flags(desc);
     int acc = accum_code(accum);
     int64_t n = w->nrows;
+    if (may_join) {
+        const PendingOp &a = g.pending[0];
+        if (!f.comp && !f.replace && w->type->code == a.xcode && n == a.n && w->vals && w->kind != K_MATRIX) {
+            PendingOp &p = g.pending[1];
+            p.kind = 2; p.w = w; p.u = p.v = nullptr; p.op = 0; p.xcode = a.xcode; p.n = n; p.xbits = 0; p.is_union = false;
+            GRB_TYPE_SWITCH(w->type->code, W, { W xv = host_cast<W, T>(x); memcpy(&p.xbits, &xv, sizeof(W)); });
+            p.set_present = !(w->nvals_known && w->nvals == n);
+            g.pending_n = 2;
+            w->nvals = n; w->nvals_known = true; w->list_valid = false;
+            return GrB_SUCCESS;
+        }
+        pending_flush();
+    }
     // value in w's type (C typecast rules, on the host: no device round trip, no synchronisation)
     char hx[8];
     (void)xcode;
@@ -234,9 +250,77 @@ __global__ void __launch_bounds__(256) k_ewise_full(const X *u, const X *v, int 
         for (int64_t i = nvec * VEC + threadIdx.x; i < n; i += blockDim.x) w[i] = binop_rt<X>(op, u[i], v[i]);
 }
 
+// the deferred pair in one pass: w = u op v, then r = x (r may be u, v or w: a thread reads its elements before it writes them)
+template <class X>
+__global__ void __launch_bounds__(256) k_lazy_pair(const X *u, const X *v, int op, X *w, X *r, uint8_t *rp, X x, int64_t n) {
+    constexpr int VEC = 16 / sizeof(X);
+    const int64_t nvec = n / VEC;
+    X xs[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; k++) xs[k] = x;
+    uint4 fill;
+    memcpy(&fill, xs, 16);
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nvec; q += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 a = reinterpret_cast<const uint4 *>(u)[q], b = reinterpret_cast<const uint4 *>(v)[q];
+        X xa[VEC], ya[VEC], z[VEC];
+        memcpy(xa, &a, 16); memcpy(ya, &b, 16);
+#pragma unroll
+        for (int k = 0; k < VEC; k++) z[k] = binop_rt<X>(op, xa[k], ya[k]);
+        uint4 o;
+        memcpy(&o, z, 16);
+        reinterpret_cast<uint4 *>(w)[q] = o;
+        reinterpret_cast<uint4 *>(r)[q] = fill;
+        if (rp) {
+#pragma unroll
+            for (int k = 0; k < VEC; k++) rp[q * VEC + k] = 1;
+        }
+    }
+    if (blockIdx.x == 0)
+        for (int64_t i = nvec * VEC + threadIdx.x; i < n; i += blockDim.x) {
+            w[i] = binop_rt<X>(op, u[i], v[i]);
+            r[i] = x;
+            if (rp) rp[i] = 1;
+        }
+}
+
+static void pending_run_ewise(const PendingOp &p) {
+    GRB_TYPE_SWITCH(p.xcode, X, {
+        GRB_LAUNCH(p.is_union ? "ewise_add" : "ewise_mult", k_ewise_full<X>, ew_grid(cdiv(p.n, 16 / (int)sizeof(X))), 256, 0,
+                   (const X *)p.u->vals, (const X *)p.v->vals, p.op, (X *)p.w->vals, p.n);
+    });
+}
+static void pending_run_fill(const PendingOp &p) {
+    GRB_TYPE_SWITCH(p.xcode, X, {
+        X xv; memcpy(&xv, &p.xbits, sizeof(X));
+        EpiArgs<X> e;
+        e.w_out = (X *)p.w->vals; e.wp_out = p.w->present; e.w_in = e.w_out; e.wp_in = e.wp_out;
+        e.mask_p = nullptr; e.mask_v = nullptr; e.mask_vsize = 0; e.mask_fp = 0; e.comp = 0; e.replace = 0; e.accum = -1;
+        e.count = nullptr;
+        GRB_LAUNCH("assign_scalar", k_assign_scalar<X>, ew_grid4(p.n), 256, 0, e, xv, p.n);
+    });
+}
+void pending_flush() {
+    const int np = g.pending_n;
+    if (!np) return;
+    g.pending_n = 0;               // (the launches below go through no entry point: nothing can re-enter)
+    const PendingOp &a = g.pending[0];
+    if (np == 2) {
+        const PendingOp &b = g.pending[1];
+        GRB_TYPE_SWITCH(a.xcode, X, {
+            X xv; memcpy(&xv, &b.xbits, sizeof(X));
+            GRB_LAUNCH("ewise_fill_pair", k_lazy_pair<X>, ew_grid(cdiv(a.n, 16 / (int)sizeof(X))), 256, 0,
+                       (const X *)a.u->vals, (const X *)a.v->vals, a.op, (X *)a.w->vals, (X *)b.w->vals,
+                       b.set_present ? b.w->present : (uint8_t *)nullptr, xv, a.n);
+        });
+        return;
+    }
+    if (a.kind == 1) pending_run_ewise(a); else pending_run_fill(a);
+}
+
 static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_BinaryOp accum, const GrB_BinaryOp op,
                          const GrB_Vector u_, const GrB_Vector v_, const GrB_Descriptor desc, bool is_union) {
     require_init();
+    if (g.pending_n) pending_flush();          // an element-wise product only ever STARTS a deferred pair
     GB_Object *w = obj_check(w_, "w"), *u = obj_check(u_, "u"), *v = obj_check(v_, "v");
     GB_Object *mask = mask_ ? obj_check(mask_, "mask") : nullptr;
     if (!op) grb_throw(GrB_NULL_POINTER, "op is NULL");
@@ -257,6 +341,14 @@ static void vector_ewise(GrB_Vector w_, const GrB_Vector mask_, const GrB_Binary
         const bool known_full = !mask && !f.comp && u->nvals_known && v->nvals_known && u->nvals == n && v->nvals == n;
         if (known_full && acc < 0 && !cmp && n > 0) {
             const bool w_was_full = w->nvals_known && w->nvals == n;
+            if (lazy_on() && w_was_full && !uc && !vc) {      // deferred: runs with the next entry point (grb_internal.cuh)
+                PendingOp &p = g.pending[0];
+                p.kind = 1; p.w = w; p.u = u; p.v = v; p.op = op->op; p.xcode = xcode; p.n = n; p.xbits = 0; p.set_present = false;
+                p.is_union = is_union;
+                g.pending_n = 1;
+                w->list_valid = false;
+                return;
+            }
             GRB_TYPE_SWITCH(xcode, X, {
                 GRB_LAUNCH(is_union ? "ewise_add" : "ewise_mult", k_ewise_full<X>, ew_grid(cdiv(n, 16 / (int)sizeof(X))), 256, 0,
                            (const X *)uv, (const X *)vv, op->op, (X *)w->vals, n);
@@ -449,14 +541,14 @@ extern "C" {
 GrB_Info GrB_Vector_eWiseMult_BinaryOp(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
                                        const GrB_BinaryOp op, const GrB_Vector u, const GrB_Vector v,
                                        const GrB_Descriptor desc) {
-    API_BEGIN
+    API_BEGIN_NOFLUSH
     vector_ewise(w, mask, accum, op, u, v, desc, false);
     API_END(w)
 }
 GrB_Info GrB_Vector_eWiseAdd_BinaryOp(GrB_Vector w, const GrB_Vector mask, const GrB_BinaryOp accum,
                                       const GrB_BinaryOp op, const GrB_Vector u, const GrB_Vector v,
                                       const GrB_Descriptor desc) {
-    API_BEGIN
+    API_BEGIN_NOFLUSH
     vector_ewise(w, mask, accum, op, u, v, desc, true);
     API_END(w)
 }

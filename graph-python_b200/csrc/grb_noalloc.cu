@@ -67,6 +67,7 @@ extern "C" GrB_Info GxB_b200_mxv_plus_times_FP32_noalloc(float *w, uint8_t *w_pr
                                                          const float *u, GrB_Index nrows, GrB_Index ncols, GrB_Index nvals,
                                                          const char **error) {
     if (error) *error = "";
+    if (g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return fail(error, e.info, "GxB_b200_mxv_plus_times_FP32_noalloc: deferred work failed"); } }
     if (!w || !w_present || !rowptr || (nvals && (!colidx || !values || !u)))
         return fail(error, GrB_NULL_POINTER, "GxB_b200_mxv_plus_times_FP32_noalloc: w, w_present, rowptr, colidx, values or u is NULL");
     if (nvals > (GrB_Index)NOALLOC_MAX_NVALS)

@@ -263,6 +263,7 @@ GrB_Info GxB_b200_peer_reduce_scatter_FP32(float *out, float *out_scaled, const 
                                            uint64_t multicast_base, uint64_t data_offset_bytes, uint64_t count,
                                            uint64_t flag_offset_bytes, int world, int rank, uint32_t seq,
                                            float *fill, uint64_t fill_count, float fill_value, int ctas, void *stream) {
+    if (g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return e.info; } }   // raw pointers: materialise first
     if ((fill_count & 3) || ((uintptr_t)fill & 15)) return GrB_INVALID_VALUE;
     if (!out || !peer_bases || (out_scaled && !div)) return GrB_NULL_POINTER;
     if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world) return GrB_INVALID_VALUE;
@@ -320,6 +321,7 @@ GrB_Info GxB_b200_peer_exchange_fused_FP32(float *out, float *out_scaled, const 
                                            uint64_t flag_offset_bytes, int world, int rank, uint32_t seq,
                                            const uint64_t *progress, const uint64_t *expected, uint64_t product_seq,
                                            float *fill, uint64_t fill_count, float fill_value, int ctas, void *stream) {
+    if (g.pending_n) { try { pending_flush(); } catch (const GrbError &e) { return e.info; } }   // raw pointers: materialise first
     if (!out || !peer_bases || (out_scaled && !div) || !progress || !expected) return GrB_NULL_POINTER;
     if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || (count & 3) || (fill_count & 3)) return GrB_INVALID_VALUE;
     if ((data_offset_bytes & 15) || (flag_offset_bytes & 3) || ((uintptr_t)out & 15) || ((uintptr_t)fill & 15) ||

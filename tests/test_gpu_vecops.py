@@ -260,3 +260,57 @@ def test_fused_isequal_matches_reference_semantics(gb):
     assert a.isequal(i32) and not a.isequal(i32, check_dtype=True)
     e1, e2 = Vector("FP32", 10), Vector("FP32", 10)
     assert e1.isequal(e2)
+
+
+# ---- the deferred element-wise pair of non-blocking mode (csrc/grb_internal.cuh PendingOp): `w << u.ewise_mult(v)` followed by a
+# ---- plain fill `r[:] << x` runs as ONE kernel at the next entry point; results are what two separate statements give
+@pytest.mark.parametrize("dt", ["FP32", "FP64", "INT32"])
+@pytest.mark.parametrize("n", [1000, 4099])
+def test_deferred_ewise_fill_pair(gb, dt, n):
+    from graphblas_b200 import binary
+
+    rng = np.random.default_rng(n)
+    npdt = O.NP_TYPES[dt]
+    a = (rng.random(n) * 9 + 1).astype(npdt)
+    d = (rng.random(n) * 3 + 1).astype(npdt)
+    op, ref = (binary.truediv, a / d) if dt.startswith("FP") else (binary.times, a * d)
+    r, dv = gb.Vector.from_dense(a), gb.Vector.from_dense(d)
+    w = gb.Vector.from_dense(np.zeros(n, dtype=npdt))
+    l0 = gb.launch_count()
+    w << r.ewise_mult(dv, op)
+    r[:] << 7
+    assert gb.launch_count() == l0                      # both wait for the next entry point ...
+    wv, wp = w.to_dense()                               # ... which is this one
+    assert gb.launch_count() - l0 >= 1
+    rv, rp = r.to_dense()
+    assert wp.all() and rp.all() and r.nvals == n
+    np.testing.assert_allclose(wv, ref.astype(npdt), rtol=1e-6)
+    assert (rv == 7).all()
+    # one fused launch: check on a fresh pair with nothing else in between
+    w << r.ewise_mult(dv, op)
+    r[:] << 3
+    l1 = gb.launch_count()
+    gb.sync()
+    assert gb.launch_count() - l1 == 1 and gb.last_kernel() == "ewise_fill_pair"
+    # aliases: the product in place, then the fill over the same vector
+    w << w.ewise_mult(dv, op)
+    w[:] << 5
+    assert (w.to_dense()[0] == 5).all()
+    # a product alone is flushed by whatever comes next; a fill into a vector that was not full sets its presence
+    w << r.ewise_mult(dv, op)
+    np.testing.assert_allclose(w.to_dense()[0], (np.full(n, 3, dtype=npdt) / d if dt.startswith("FP") else np.full(n, 3, dtype=npdt) * d).astype(npdt), rtol=1e-6)
+    e = gb.Vector(dt, n)
+    w << r.ewise_mult(dv, op)
+    e[:] << 2
+    ev, ep = e.to_dense()
+    assert ep.all() and (ev == 2).all() and e.nvals == n
+    # switched off: two launches, same results
+    gb.set_option("lazy", 0)
+    try:
+        l2 = gb.launch_count()
+        w << r.ewise_mult(dv, op)
+        r[:] << 9
+        assert gb.launch_count() - l2 == 2
+        assert (r.to_dense()[0] == 9).all()
+    finally:
+        gb.set_option("lazy", 1)
