@@ -1040,6 +1040,13 @@ def run_b200(args):
                                       "CUDA events around every launch in a second pass of the same steps (events between the product and "
                                       "the exchange kernel launched behind it would serialise them)"},
     }
+    if world > 1 and job.partition in ("peer", "fused", "col"):
+        rows_b, ent_b = job.out_rows * (8 + 4 + 4), job.nnz_local * (4 + 4 + 4)
+        line["roofline"]["note"] = (f"column block: SURVEY 8d's per-row term (row pointer + y write + accumulator read = 16 B) is charged for all "
+                                    f"{job.out_rows} output rows of this rank's partial product ({rows_b / 1e6:.0f} MB of {(rows_b + ent_b) / 1e6:.0f} MB); "
+                                    "k_spmv_red reads no row pointers (flagged stream form) and its REDs resolve in L2, so at N > 1 this fraction "
+                                    "overstates the kernel; the N = 1 line is its figure of merit")
+        line["roofline"]["frac_entries_only"] = (ent_b * products / (k_ms * 1e-3) / 1e9 / peak) if k_cnt else None
     # dram__bytes of the dominant kernel come from an ncu capture, which bench.py cannot take itself: the committed figure is
     # quoted only for the exact launch it was captured on (same scale, one GPU, same kernel); anything else says null
     traffic_file = os.path.join(ROOT, "profiles", "spmv_pull_traffic.json")
