@@ -161,6 +161,8 @@ GrB_Info GrB_Matrix_dup(GrB_Matrix *C, const GrB_Matrix A) {
 GrB_Info GrB_Matrix_free(GrB_Matrix *A) {
     if (!A || !*A) return GrB_SUCCESS;
     GB_Object *o = (GB_Object *)*A;
+    // deferred element-wise work may name this object (grb_internal.cuh PendingOp): run it before the storage goes away
+    if (g.pending_n) { try { pending_flush(); } catch (const GrbError &) { g.pending_n = 0; } }
     if (o->magic == GRB_MAGIC) obj_free(o);
     *A = nullptr;
     return GrB_SUCCESS;
