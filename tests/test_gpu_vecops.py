@@ -304,6 +304,15 @@ def test_deferred_ewise_fill_pair(gb, dt, n):
     e[:] << 2
     ev, ep = e.to_dense()
     assert ep.all() and (ev == 2).all() and e.nvals == n
+    # an object named by deferred work may be freed before anything else happens: the free runs the work first
+    tmp = gb.Vector.from_dense(np.zeros(n, dtype=npdt))
+    tmp << r.ewise_mult(dv, op)
+    del tmp
+    import gc
+
+    gc.collect()
+    gb.sync()
+    assert (r.to_dense()[0] == 3).all()
     # switched off: two launches, same results
     gb.set_option("lazy", 0)
     try:
