@@ -61,7 +61,8 @@ def parse_args():
     ap.add_argument("--peer-ctas", type=int, default=0, help="CTAs of the peer exchange kernel (0 = 148 fused / 296 peer)")
     ap.add_argument("--workload", default="pagerank", choices=["pagerank", "sssp", "cc", "fastsv", "spgemm", "tc", "bfs"],
                     help="pagerank = the contract line (BASELINE configs[1]); sssp = Bellman-Ford min_plus INT64 to the fixed point, "
-                         "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling)")
+                         "row-sharded over --gpus ranks at a FIXED --scale (BASELINE configs[2], strong scaling); bfs = level BFS any_pair "
+                         "(BASELINE configs[0]'s statement) with the vertices in blocks over --gpus ranks, push and pull per level")
     ap.add_argument("--no-spgemm", action="store_true", help="skip the SpGEMM leg (BASELINE configs[4]: A.mxm(A) FP64, scale 20) of the line")
     ap.add_argument("--spgemm-scale", type=int, default=20)
     ap.add_argument("--extra", action="store_true", help="also time the other BASELINE configs (extra keys)")
@@ -1815,8 +1816,9 @@ class BfsJob:
 
 
 def measure_bfs_sharded(gb, scale, rank, world, reps=5, breakdown=False):
-    """Level BFS with the source vertices sharded over `world` GPUs (BfsJob): device time of one traversal (max over ranks), TEPS by
-    the Graph500 convention, and bit-exact parity with the one-GPU traversal of the same graph, asserted.  Rank 0 returns the dict."""
+    """Level BFS with the vertices in 1-D blocks over `world` GPUs (BfsJob: push and pull per level): device time of one traversal
+    (max over ranks), TEPS by the Graph500 convention, and bit-exact parity with the one-GPU traversal of the same graph,
+    asserted.  Rank 0 returns the dict."""
     import torch
     import torch.distributed as dist
 
@@ -1828,7 +1830,7 @@ def measure_bfs_sharded(gb, scale, rank, world, reps=5, breakdown=False):
         torch.cuda.synchronize()
 
     for _ in range(2):
-        job.step()                                             # warm-up: cached transpose of the block, NCCL channels
+        job.step()                                             # warm-up: the library's cached forms, NCCL channels
     ok = job.check()
     times = []
     l0 = gb.launch_count()
