@@ -427,6 +427,13 @@ def _np_index(idx):
     return np.ascontiguousarray(idx, dtype=np.uint64)
 
 
+def _slice_index(key, size):
+    """The GrB_Index list a Python slice stands for on a vector of `size` (the reference resolves slices to GrB_ALL, a
+    (lo, hi, stride) triple or a list, core/utils.py / core/expr.py AmbiguousAssignOrExtract; this library takes GrB_ALL or a list).
+    Negative steps give the indices in the order the slice visits them, as numpy does."""
+    return np.arange(*key.indices(int(size)), dtype=np.int64).astype(np.uint64)
+
+
 def _buf(arr, ctype):
     return ffi.cast(ctype, ffi.from_buffer(arr)) if arr.size else ffi.cast(ctype, 0)
 
@@ -640,6 +647,8 @@ class Vector(BaseType):
     def __getitem__(self, key):
         if isinstance(key, slice) and key == slice(None):
             return _Assigner(Updater(self), key)
+        if isinstance(key, slice):
+            return _IndexedVector(self, _slice_index(key, self._size))
         if isinstance(key, (list, tuple, np.ndarray)):
             return _IndexedVector(self, _np_index(key))
         if isinstance(key, Vector):
@@ -652,7 +661,7 @@ class Vector(BaseType):
         return _ScalarResult(s)
 
     def __setitem__(self, key, value):
-        if (isinstance(key, slice) and key == slice(None)) or isinstance(key, (list, tuple, np.ndarray, Vector)):
+        if isinstance(key, (slice, list, tuple, np.ndarray, Vector)):
             self._assign(key, value, opts={})
         else:
             call(f"GrB_Vector_setElement_{self.dtype.name}", [self, self.dtype.np_type.type(value).item(), int(key)])
@@ -698,6 +707,9 @@ class Vector(BaseType):
         I is `:` (GrB_ALL) or an index list."""
         if isinstance(key, slice) and key == slice(None):
             I, ni, keep = lib.GrB_ALL, self._size, None
+        elif isinstance(key, slice):
+            keep = _slice_index(key, self._size)          # w[lo:hi:step]: the index list the slice stands for
+            I, ni = _buf(keep, "GrB_Index*"), keep.size
         elif isinstance(key, (list, tuple, np.ndarray)):
             keep = _np_index(key)
             I, ni = _buf(keep, "GrB_Index*"), keep.size
@@ -714,7 +726,7 @@ class Vector(BaseType):
             call("GxB_b200_Vector_assign_Vector", [self, mask, accum, value, key, _descriptor(replace_, comp, structure, **opts)])
             return
         else:
-            raise NotImplementedError("assignment takes w[:], w[index list] or w[index vector]")
+            raise TypeError("assignment takes w[:], w[slice], w[index list] or w[index vector]")
         comp = structure = False
         if mask is not None:
             comp, structure = mask.complement, mask.structure
